@@ -1,0 +1,196 @@
+/* rt_b200.h — C ABI of the B200-native per-pixel render path.
+ *
+ * Drop-in boundary: the reference has no FFI layer; the seam this library replaces is the
+ * C++ call `tracer.render(framebuffer)` in raytracer/src/main.cpp:74-82 (Tracer::render,
+ * raytracer/src/tracer.cpp:247-305) together with the loader call that builds its inputs
+ * (jsonio::load_scene_from_json, raytracer/src/json_loader.cpp:499-504).  INTEGRATION.md shows
+ * the ~20-line change to the reference's main.cpp that binds these entry points.
+ *
+ * Conventions: every function returns RT_OK (0) or a negative rt_status; the message of the
+ * last failure on the calling thread is rt_last_error().  No C++ exception crosses this ABI.
+ * All pointers are plain host pointers unless the name says `_device`.  The caller owns every
+ * host buffer; device memory is owned by the library.  There is no CPU fallback: without a
+ * CUDA device every compute entry point fails with RT_ERR_CUDA.
+ */
+#ifndef RT_B200_H
+#define RT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum rt_status {
+    RT_OK = 0,
+    RT_ERR_ARG = -1,      /* null/invalid argument */
+    RT_ERR_IO = -2,       /* file could not be opened / written           (main.cpp exit code 4 for PNG) */
+    RT_ERR_PARSE = -3,    /* JSON parse / processing error                 (main.cpp exit code 3)       */
+    RT_ERR_LIMIT = -4,    /* scene exceeds a compiled-in device limit (CSG nesting, recursion depth)   */
+    RT_ERR_CUDA = -5,     /* CUDA runtime failure or no device                                           */
+    RT_ERR_STATE = -6     /* call order (e.g. render before init)                                        */
+} rt_status;
+
+/* RenderMode (raytracer/src/tracer.h:8-11) */
+enum { RT_MODE_STANDARD = 0, RT_MODE_PAPER = 1 };
+
+/* ---------------------------------------------------------------------------------------------
+ * Flat scene description = output of the host scene compiler, input of rt_scene_upload.
+ * Everything is plain-old-data; doubles are kept only where the primary-ray set-up needs them.
+ * ------------------------------------------------------------------------------------------- */
+
+/* Material (raytracer/src/geometry.h:5-22) after json_loader.cpp:83-123; `ambient` is already
+ * multiplied by the scene ambient (shading.cpp:39).  kd is always 1 in loaded scenes.          */
+typedef struct rt_material {
+    float albedo[3]; float ks;
+    float ambient[3]; float kr;
+    float kt; float shininess; float ior; float kd;
+} rt_material;
+
+/* PointLight (raytracer/src/scene.h:22-27) */
+typedef struct rt_light { float pos[3]; float pad0; float intensity[3]; float pad1; } rt_light;
+
+/* Primitive kinds and flags */
+enum { RT_PRIM_SPHERE = 0, RT_PRIM_HALFSPACE = 1, RT_PRIM_POKEBALL = 2, RT_PRIM_PROGRAM = 3 };
+enum {
+    RT_FLAG_XFORMED = 1,  /* at least one transform node above: front_face is re-derived from the oriented
+                             normal (transform.cpp:41,63-64), half-space +-inf endpoints collapse to t=0      */
+    RT_FLAG_AFFINE  = 2,  /* sphere/pokeball under a non-uniform scaling: solved in its local frame via `xf`  */
+    RT_FLAG_WRAPPED = 4,  /* top-level object is a transform node: child queried on [0,inf], then the hit is
+                             accepted only for tmin < t < tmax (transform.cpp:29,38)                           */
+    RT_FLAG_NEVER   = 8   /* degenerate scaling (|s| < 1e-6) above: never hit (transform.cpp:103)              */
+};
+
+/* One primitive record.  Used both for top-level objects (scene.objects order = JSON order) and
+ * for the leaves of CSG programs.
+ *   sphere / pokeball : geom = cx, cy, cz, r          (Sphere, geometry.h:79-108)
+ *   half-space        : geom = nx, ny, nz, n.p0       (HalfSpace, geometry.h:111-158; n unit)
+ *   program           : geom unused; aux = first op, xf = op count                              */
+typedef struct rt_prim {
+    float   geom[4];
+    int32_t kind;     /* RT_PRIM_*                                                     */
+    int32_t flags;    /* RT_FLAG_*                                                     */
+    int32_t mat;      /* material id; pokeball: first of 5 (top,bottom,belt,ring,button) */
+    int32_t aux;      /* pokeball: index into pokeballs[]; program: first op           */
+    int32_t xf;       /* RT_FLAG_AFFINE: index into affines[]; program: op count; else -1 */
+    int32_t pad[3];
+} rt_prim;
+
+/* Pokeball region parameters (geometry.h:161-242, geometry.cpp:163-180) with the acos removed:
+ * ang <= btnOuter  <=>  u.btnDir >= cos_outer ;  ang >= inner  <=>  u.btnDir <= cos_inner.        */
+typedef struct rt_pokeball {
+    float btn_dir[3]; float cos_outer;
+    float up[3];      float cos_inner;   /* `up` is the local +Y axis carried through baked rotations */
+    float belt_half;  float pad[3];
+} rt_pokeball;
+
+/* world -> leaf-local affine map (rows of a 3x4 matrix), for RT_FLAG_AFFINE leaves */
+typedef struct rt_affine { float m[3][4]; } rt_affine;
+
+/* CSG program = postfix evaluation of a csg / transform subtree (csg.cpp:61-163):
+ *   RT_OP_LEAF          acc = interval(leaf arg)
+ *   RT_OP_COMBINE_LEAF  acc = acc (op) interval(leaf arg)
+ *   RT_OP_PUSH          push acc
+ *   RT_OP_COMBINE_POP   acc = pop (op) acc
+ *   RT_OP_XFIX          a transform node sat here: non-finite endpoints -> 0 (transform.cpp:79-80);
+ *                       arg != 0xFFFFF: zero normals become fallbacks[arg] (core.h:58-64 via
+ *                       transform.cpp:117-118,201-203)
+ * word = opcode | csg_op << 4 | arg << 8                                                           */
+enum { RT_OP_LEAF = 0, RT_OP_COMBINE_LEAF = 1, RT_OP_PUSH = 2, RT_OP_COMBINE_POP = 3, RT_OP_XFIX = 4 };
+enum { RT_CSG_UNION = 0, RT_CSG_INTERSECTION = 1, RT_CSG_DIFFERENCE = 2 };
+#define RT_OP_WORD(opcode, csg, arg) ((uint32_t)(opcode) | ((uint32_t)(csg) << 4) | ((uint32_t)(arg) << 8))
+#define RT_MAX_CSG_STACK 8      /* right-nesting depth of a CSG program                   */
+#define RT_MAX_RECURSION 16     /* medium.recursion above this is rejected (RT_ERR_LIMIT) */
+
+typedef struct rt_scene_desc {
+    /* camera + screen (camera.h:8-36); kept in double so primary rays are rounded once */
+    double eye[3]; double screen_p[3]; double lx, ly;
+    int32_t width, height;                       /* ScreenSpec::nx(), ny() (camera.h:19-21) */
+    /* medium (scene.h:40-47) */
+    float background[3]; float medium_index;
+    int32_t recursion;
+    int32_t n_objects, n_leaves, n_pokeballs, n_affines, n_ops, n_materials, n_lights, n_fallbacks;
+    const rt_prim*     objects;     /* top-level, JSON order */
+    const rt_prim*     leaves;      /* leaves of CSG programs */
+    const rt_pokeball* pokeballs;
+    const rt_affine*   affines;
+    const uint32_t*    ops;
+    const rt_material* materials;
+    const rt_light*    lights;
+    const float*       fallbacks;   /* n_fallbacks x 4 floats (unit normal, pad) */
+} rt_scene_desc;
+
+typedef struct rt_scene rt_scene;          /* a scene resident on the device(s) */
+typedef struct rt_compiled rt_compiled;    /* host-side compiled scene (owns an rt_scene_desc) */
+
+/* Per-render statistics (device counters + CUDA-event timing). */
+typedef struct rt_stats {
+    double kernel_ms;          /* trace (+ post-process) kernels, CUDA events on the render stream */
+    double total_ms;           /* whole rt_render call incl. copies, host clock                     */
+    uint64_t primary_rays;     /* Scene::intersect-equivalent queries for camera rays               */
+    uint64_t shadow_rays;      /* Scene::occluded-equivalent queries                                 */
+    uint64_t secondary_rays;   /* reflection + refraction closest-hit queries                        */
+    uint64_t prim_tests;       /* primitive tests executed (sphere/plane/pokeball/leaf)              */
+    int32_t width, height, samples_per_pixel, n_tiles;
+} rt_stats;
+
+/* ---- library / device ---------------------------------------------------------------------- */
+/* Select the CUDA device this process renders on (one process per GPU).  device < 0: current. */
+int rt_init(int device);
+void rt_shutdown(void);
+const char* rt_last_error(void);
+const char* rt_version(void);
+
+/* ---- host scene compiler (replaces jsonio::load_scene_from_json[_text], json_loader.cpp:458-504) */
+int rt_compile_json_text(const char* json_text, rt_compiled** out);
+int rt_compile_json_file(const char* path, rt_compiled** out);
+const rt_scene_desc* rt_compiled_desc(const rt_compiled*);
+void rt_compiled_free(rt_compiled*);
+
+/* ---- device scene ---------------------------------------------------------------------------- */
+int rt_scene_upload(const rt_scene_desc* desc, rt_scene** out);
+void rt_scene_free(rt_scene*);
+int rt_scene_size(const rt_scene*, int* width, int* height);
+
+/* ---- render (replaces Tracer::render, tracer.cpp:247-305) ------------------------------------
+ * Tiles are runs of RT_TILE_PIXELS consecutive pixels in the reference's loop order
+ * (standard: y outer from the BOTTOM row, x inner; paper: rows from the top); a rank renders
+ * tiles rank, rank+world, ... (interleaved).  world = 1 renders the whole frame.
+ *
+ * rt_render: host outputs, any of which may be NULL.
+ *   rgb8   : H*W*3 bytes, row 0 = top, R,G,B = toByte(channel) (core.h:313-316; main.cpp:19-34 minus
+ *            OpenCV's BGR swap)
+ *   rgbf   : H*W*3 floats, the linear framebuffer Tracer::render fills
+ *   ids    : H*W*S int32 primary-hit codes (object*8 + pokeball region, -1 miss), S = 8 / 1
+ *   With world > 1 only this rank's pixels are written (others left untouched).                  */
+#define RT_TILE_PIXELS 156
+int rt_render(rt_scene*, int mode, int rank, int world,
+              uint8_t* rgb8, float* rgbf, int32_t* ids, rt_stats* stats);
+
+/* Same, but the frame stays on the device: rgba8_device is H*W uchar4 (A = 255), rgbf_device is
+ * H*W float4 (may be NULL), ids_device H*W*S int32 (may be NULL).  `stream` is a cudaStream_t
+ * (NULL = the library's stream).  Used by the multi-GPU harness, which gathers the slices with NCCL. */
+int rt_render_device(rt_scene*, int mode, int rank, int world,
+                     void* rgba8_device, void* rgbf_device, void* ids_device,
+                     void* stream, rt_stats* stats);
+
+/* Known-answer entry point: trace n arbitrary rays (6 doubles each: origin, direction) through
+ * Scene::intersect(1e-4, inf) + Tracer::trace; out = 16 doubles per ray:
+ *   hit, t, p[3], n[3], front_face, code, r, g, b, occluded on (1e-3, 5], 2 pad.                  */
+int rt_trace_rays(rt_scene*, int n, const double* rays, double* out);
+
+/* First n jitter pairs of the Standard loop starting at sample `first_sample` (tracer.cpp:284-293),
+ * produced by the DEVICE generator; out = 2n doubles (dx, dy).                                   */
+int rt_debug_jitter(uint64_t first_sample, int n, double* out);
+
+/* Measured FP32 FFMA peak of the current device in TFLOP/s (dependent-free FFMA micro-benchmark). */
+int rt_measure_fp32_peak(double* tflops);
+
+/* ---- PNG (replaces cv::imwrite in main.cpp:84-89) ------------------------------------------- */
+int rt_write_png_rgb8(const char* path, const uint8_t* rgb8, int width, int height);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RT_B200_H */

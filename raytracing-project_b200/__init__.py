@@ -1,0 +1,262 @@
+"""raytracing-project_b200 — host-side mirror (Python) of the reference's render interface over the
+C ABI in include/rt_b200.h.
+
+The reference's public surface for the hot path is ``jsonio::load_scene_from_json`` +
+``Tracer{scene,camera,width,height,mode}.render(framebuffer)`` (raytracer/src/json_loader.h:27-36,
+raytracer/src/tracer.h:18-35).  The same names are kept here:
+
+    scene = load_scene_from_json("examples/pokeballs.json")      # or load_scene_from_json_text(text)
+    fb = Tracer(scene, mode=RenderMode.Standard).render()         # float32 [H, W, 3], row 0 = top
+
+The product's own host language is C++17 (csrc/ray_main.cpp is the CLI); this module exists so the
+parity tests and bench.py can call the very same shared library.  There is NO CPU fallback: if
+``librt_b200.so`` is missing or no CUDA device is present every render call raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import enum
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "librt_b200.so")
+RAY_CLI = os.path.join(_HERE, "ray")
+TILE_PIXELS = 156
+PAPER_ROWS = 16
+
+
+class RtError(RuntimeError):
+    def __init__(self, code: int, message: str):
+        super().__init__(f"rt_b200 error {code}: {message}")
+        self.code = code
+        self.message = message
+
+
+class RenderMode(enum.IntEnum):      # tracer.h:8-11
+    Standard = 0
+    Paper = 1
+
+
+class RtStats(C.Structure):
+    _fields_ = [("kernel_ms", C.c_double), ("total_ms", C.c_double),
+                ("primary_rays", C.c_uint64), ("shadow_rays", C.c_uint64), ("secondary_rays", C.c_uint64),
+                ("prim_tests", C.c_uint64),
+                ("width", C.c_int32), ("height", C.c_int32), ("samples_per_pixel", C.c_int32), ("n_tiles", C.c_int32)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+class RtPrim(C.Structure):
+    _fields_ = [("geom", C.c_float * 4), ("kind", C.c_int32), ("flags", C.c_int32), ("mat", C.c_int32),
+                ("aux", C.c_int32), ("xf", C.c_int32), ("pad", C.c_int32 * 3)]
+
+
+class RtMaterial(C.Structure):
+    _fields_ = [("albedo", C.c_float * 3), ("ks", C.c_float), ("ambient", C.c_float * 3), ("kr", C.c_float),
+                ("kt", C.c_float), ("shininess", C.c_float), ("ior", C.c_float), ("kd", C.c_float)]
+
+
+class RtLight(C.Structure):
+    _fields_ = [("pos", C.c_float * 3), ("pad0", C.c_float), ("intensity", C.c_float * 3), ("pad1", C.c_float)]
+
+
+class RtPokeball(C.Structure):
+    _fields_ = [("btn_dir", C.c_float * 3), ("cos_outer", C.c_float), ("up", C.c_float * 3), ("cos_inner", C.c_float),
+                ("belt_half", C.c_float), ("pad", C.c_float * 3)]
+
+
+class RtAffine(C.Structure):
+    _fields_ = [("m", (C.c_float * 4) * 3)]
+
+
+class RtSceneDesc(C.Structure):
+    _fields_ = [("eye", C.c_double * 3), ("screen_p", C.c_double * 3), ("lx", C.c_double), ("ly", C.c_double),
+                ("width", C.c_int32), ("height", C.c_int32),
+                ("background", C.c_float * 3), ("medium_index", C.c_float),
+                ("recursion", C.c_int32),
+                ("n_objects", C.c_int32), ("n_leaves", C.c_int32), ("n_pokeballs", C.c_int32), ("n_affines", C.c_int32),
+                ("n_ops", C.c_int32), ("n_materials", C.c_int32), ("n_lights", C.c_int32), ("n_fallbacks", C.c_int32),
+                ("objects", C.POINTER(RtPrim)), ("leaves", C.POINTER(RtPrim)), ("pokeballs", C.POINTER(RtPokeball)),
+                ("affines", C.POINTER(RtAffine)), ("ops", C.POINTER(C.c_uint32)), ("materials", C.POINTER(RtMaterial)),
+                ("lights", C.POINTER(RtLight)), ("fallbacks", C.POINTER(C.c_float))]
+
+
+# every symbol include/rt_b200.h declares (tests/test_abi.py checks the list against the header)
+ABI_SYMBOLS = [
+    "rt_init", "rt_shutdown", "rt_last_error", "rt_version",
+    "rt_compile_json_text", "rt_compile_json_file", "rt_compiled_desc", "rt_compiled_free",
+    "rt_scene_upload", "rt_scene_free", "rt_scene_size",
+    "rt_render", "rt_render_device", "rt_trace_rays", "rt_debug_jitter", "rt_measure_fp32_peak",
+    "rt_write_png_rgb8",
+]
+
+_lib = None
+
+
+def build(verbose: bool = False) -> None:
+    """Compile librt_b200.so and the `ray` CLI in-tree (nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo)."""
+    subprocess.run(["make", "-C", _HERE] + ([] if verbose else ["-s"]), check=True)
+
+
+def lib():
+    """The loaded C-ABI library.  Fails loudly when it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RtError(-6, f"{LIB_PATH} is missing: run `make -C {_HERE}` (there is no fallback path)")
+        L = C.CDLL(LIB_PATH)
+        L.rt_last_error.restype = C.c_char_p
+        L.rt_version.restype = C.c_char_p
+        L.rt_init.argtypes = [C.c_int]
+        L.rt_compile_json_text.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
+        L.rt_compile_json_file.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
+        L.rt_compiled_desc.restype = C.POINTER(RtSceneDesc)
+        L.rt_compiled_desc.argtypes = [C.c_void_p]
+        L.rt_compiled_free.argtypes = [C.c_void_p]
+        L.rt_scene_upload.argtypes = [C.POINTER(RtSceneDesc), C.POINTER(C.c_void_p)]
+        L.rt_scene_free.argtypes = [C.c_void_p]
+        L.rt_scene_size.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.rt_render.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(RtStats)]
+        L.rt_render_device.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+                                       C.c_void_p, C.POINTER(RtStats)]
+        L.rt_trace_rays.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        L.rt_debug_jitter.argtypes = [C.c_uint64, C.c_int, C.c_void_p]
+        L.rt_measure_fp32_peak.argtypes = [C.POINTER(C.c_double)]
+        L.rt_write_png_rgb8.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_int]
+        _lib = L
+    return _lib
+
+
+def _check(rc: int) -> None:
+    if rc != 0:
+        raise RtError(rc, lib().rt_last_error().decode(errors="replace"))
+
+
+def init(device: int = -1) -> None:
+    _check(lib().rt_init(device))
+
+
+def shutdown() -> None:
+    lib().rt_shutdown()
+
+
+class Scene:
+    """A compiled scene (host) and, once a render is asked for, its device copy.
+
+    Mirrors what jsonio::load_scene_from_json fills (Scene + Camera, json_loader.cpp:458-504)."""
+
+    def __init__(self, json_text: str | None = None, path: str | None = None):
+        self._compiled = C.c_void_p()
+        self._device = C.c_void_p()
+        if path is not None:
+            _check(lib().rt_compile_json_file(os.fsencode(path), C.byref(self._compiled)))
+        else:
+            _check(lib().rt_compile_json_text((json_text or "").encode(), C.byref(self._compiled)))
+        self.desc = lib().rt_compiled_desc(self._compiled).contents
+        self.width, self.height = int(self.desc.width), int(self.desc.height)
+
+    # -- flat description, for the host-logic tests ---------------------------------------------
+    def objects(self):
+        return [self.desc.objects[i] for i in range(self.desc.n_objects)]
+
+    def leaves(self):
+        return [self.desc.leaves[i] for i in range(self.desc.n_leaves)]
+
+    def ops(self):
+        return [int(self.desc.ops[i]) for i in range(self.desc.n_ops)]
+
+    def materials(self):
+        return [self.desc.materials[i] for i in range(self.desc.n_materials)]
+
+    def device_handle(self):
+        if not self._device:
+            _check(lib().rt_scene_upload(C.byref(self.desc), C.byref(self._device)))
+        return self._device
+
+    def close(self):
+        if getattr(self, "_device", None):
+            lib().rt_scene_free(self._device)
+            self._device = C.c_void_p()
+        if getattr(self, "_compiled", None):
+            lib().rt_compiled_free(self._compiled)
+            self._compiled = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def load_scene_from_json(filename: str) -> Scene:          # json_loader.h:27
+    return Scene(path=filename)
+
+
+def load_scene_from_json_text(json_text: str) -> Scene:    # json_loader.h:36
+    return Scene(json_text=json_text)
+
+
+class Tracer:
+    """Tracer (tracer.h:18-35): ``render()`` returns the linear framebuffer, row 0 = top."""
+
+    def __init__(self, scene: Scene, mode: RenderMode = RenderMode.Standard):
+        self.scene = scene
+        self.mode = RenderMode(mode)
+        self.width, self.height = scene.width, scene.height
+        self.last_stats: dict | None = None
+
+    def render(self, want_rgb8: bool = False, want_ids: bool = False, rank: int = 0, world: int = 1):
+        """Returns fb float32[H,W,3]; with want_rgb8/want_ids a dict(fb=, rgb8=uint8[H,W,3], ids=int32[H,W,S])."""
+        W, H = self.width, self.height
+        S = 1 if self.mode == RenderMode.Paper else 8
+        fb = np.zeros((H, W, 3), np.float32)
+        rgb8 = np.zeros((H, W, 3), np.uint8) if want_rgb8 else None
+        ids = np.full((H, W, S), -1, np.int32) if want_ids else None
+        st = RtStats()
+        ptr = lambda a: a.ctypes.data_as(C.c_void_p) if a is not None else None
+        _check(lib().rt_render(self.scene.device_handle(), int(self.mode), rank, world, ptr(rgb8), ptr(fb), ptr(ids), C.byref(st)))
+        self.last_stats = st.as_dict()
+        if want_rgb8 or want_ids:
+            return {"fb": fb, "rgb8": rgb8, "ids": ids}
+        return fb
+
+    def render_device(self, rgba8_ptr: int, rgbf_ptr: int = 0, ids_ptr: int = 0, stream: int = 0,
+                      rank: int = 0, world: int = 1, want_stats: bool = False):
+        """Render into caller-owned DEVICE buffers (e.g. torch tensors' data_ptr()); asynchronous unless want_stats."""
+        st = RtStats()
+        _check(lib().rt_render_device(self.scene.device_handle(), int(self.mode), rank, world,
+                                      C.c_void_p(rgba8_ptr), C.c_void_p(rgbf_ptr or None), C.c_void_p(ids_ptr or None),
+                                      C.c_void_p(stream or None), C.byref(st) if want_stats else None))
+        if want_stats:
+            self.last_stats = st.as_dict()
+        return self.last_stats
+
+    def trace_rays(self, rays: np.ndarray) -> np.ndarray:
+        """Known-answer entry point: [n,6] float64 rays -> [n,16] float64 records (see rt_b200.h)."""
+        rays = np.ascontiguousarray(rays, np.float64).reshape(-1, 6)
+        out = np.zeros((rays.shape[0], 16), np.float64)
+        _check(lib().rt_trace_rays(self.scene.device_handle(), rays.shape[0], rays.ctypes.data_as(C.c_void_p),
+                                   out.ctypes.data_as(C.c_void_p)))
+        return out
+
+
+def debug_jitter(first_sample: int, n: int) -> np.ndarray:
+    out = np.zeros((n, 2), np.float64)
+    _check(lib().rt_debug_jitter(first_sample, n, out.ctypes.data_as(C.c_void_p)))
+    return out
+
+
+def measure_fp32_peak() -> float:
+    v = C.c_double()
+    _check(lib().rt_measure_fp32_peak(C.byref(v)))
+    return float(v.value)
+
+
+def write_png_rgb8(path: str, rgb8: np.ndarray) -> None:
+    rgb8 = np.ascontiguousarray(rgb8, np.uint8)
+    H, W = rgb8.shape[:2]
+    _check(lib().rt_write_png_rgb8(os.fsencode(path), rgb8.ctypes.data_as(C.c_void_p), W, H))

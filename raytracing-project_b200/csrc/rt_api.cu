@@ -1,0 +1,453 @@
+// rt_api.cu — C ABI (include/rt_b200.h) over the sm_100a kernels.  One process renders on one
+// GPU; multi-GPU jobs run one process per GPU and gather the slices themselves (NCCL).
+// There is no CPU fallback: every compute entry point fails with RT_ERR_CUDA without a device.
+#include <chrono>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "rt_kernels.cuh"
+#include "rt_internal.hpp"
+
+namespace {
+
+int fail(int code, const std::string& msg) { rt_set_error(msg); return code; }
+#define CU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) \
+    return fail(RT_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
+
+struct Context {
+    bool ready{false};
+    int device{-1}, sms{0};
+    cudaStream_t stream{nullptr};
+    cudaEvent_t ev0{nullptr}, ev1{nullptr};
+    // jitter-stream checkpoints (scene independent)
+    uint32_t* mt_table{nullptr}; long long mt_tiles{0}, mt_capacity{0};
+    uint32_t* mt_resume{nullptr};
+    unsigned long long* counters{nullptr}; unsigned* tile_counter{nullptr};
+    const void* const_owner{nullptr};     // which scene currently occupies constant memory
+    std::mutex mu;
+};
+Context g_ctx;
+
+template <class T> int upload(const std::vector<T>& h, T** d) {
+    *d = nullptr;
+    size_t bytes = std::max<size_t>(h.size(), 1) * sizeof(T);
+    CU(cudaMalloc((void**)d, bytes));
+    if (!h.empty()) CU(cudaMemcpy(*d, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice));
+    return RT_OK;
+}
+
+}  // namespace
+
+struct rt_scene {
+    rtd::SceneHeader hdr{};
+    bool fits_const{false};
+    std::vector<float4> obj_geom, leaf_geom, pokeballs, affines, materials, lights, fallbacks;
+    std::vector<int4> obj_meta, leaf_meta, runs;
+    std::vector<uint32_t> ops;
+    float4 *d_obj_geom{nullptr}, *d_leaf_geom{nullptr}, *d_pokeballs{nullptr}, *d_affines{nullptr}, *d_materials{nullptr},
+           *d_lights{nullptr}, *d_fallbacks{nullptr};
+    int4 *d_obj_meta{nullptr}, *d_leaf_meta{nullptr}, *d_runs{nullptr};
+    uint32_t* d_ops{nullptr};
+    int width{0}, height{0};
+    // device frame buffers (lazily sized)
+    uchar4* d_rgba8{nullptr}; float4* d_rgbf{nullptr}; int* d_ids{nullptr}; rtd::GBuf* d_gbuf{nullptr};
+    unsigned char* d_pack{nullptr}; size_t pack_bytes{0}; size_t ids_elems{0};
+};
+
+namespace {
+
+int4 meta_of(const rt_prim& p) { return make_int4((p.kind & 0xff) | (p.flags << 8), p.mat, p.aux, p.xf); }
+
+void build_host_arrays(const rt_scene_desc& d, rt_scene& s) {
+    for (int i = 0; i < d.n_objects; ++i) {
+        const rt_prim& p = d.objects[i];
+        s.obj_geom.push_back(make_float4(p.geom[0], p.geom[1], p.geom[2], p.geom[3]));
+        s.obj_meta.push_back(meta_of(p));
+    }
+    for (int i = 0; i < d.n_leaves; ++i) {
+        const rt_prim& p = d.leaves[i];
+        s.leaf_geom.push_back(make_float4(p.geom[0], p.geom[1], p.geom[2], p.geom[3]));
+        s.leaf_meta.push_back(meta_of(p));
+    }
+    for (int i = 0; i < d.n_pokeballs; ++i) {
+        const rt_pokeball& b = d.pokeballs[i];
+        s.pokeballs.push_back(make_float4(b.btn_dir[0], b.btn_dir[1], b.btn_dir[2], b.cos_outer));
+        s.pokeballs.push_back(make_float4(b.up[0], b.up[1], b.up[2], b.cos_inner));
+        s.pokeballs.push_back(make_float4(b.belt_half, 0.f, 0.f, 0.f));
+    }
+    for (int i = 0; i < d.n_affines; ++i)
+        for (int r = 0; r < 3; ++r) s.affines.push_back(make_float4(d.affines[i].m[r][0], d.affines[i].m[r][1], d.affines[i].m[r][2], d.affines[i].m[r][3]));
+    for (int i = 0; i < d.n_ops; ++i) s.ops.push_back(d.ops[i]);
+    for (int i = 0; i < d.n_materials; ++i) {
+        const rt_material& m = d.materials[i];
+        s.materials.push_back(make_float4(m.albedo[0], m.albedo[1], m.albedo[2], m.ks));
+        s.materials.push_back(make_float4(m.ambient[0], m.ambient[1], m.ambient[2], m.kr));
+        s.materials.push_back(make_float4(m.kt, m.shininess, m.ior, m.kd));
+    }
+    for (int i = 0; i < d.n_lights; ++i) {
+        s.lights.push_back(make_float4(d.lights[i].pos[0], d.lights[i].pos[1], d.lights[i].pos[2], 0.f));
+        s.lights.push_back(make_float4(d.lights[i].intensity[0], d.lights[i].intensity[1], d.lights[i].intensity[2], 0.f));
+    }
+    for (int i = 0; i < d.n_fallbacks; ++i) s.fallbacks.push_back(make_float4(d.fallbacks[4 * i], d.fallbacks[4 * i + 1], d.fallbacks[4 * i + 2], 0.f));
+    // runs of consecutive plain primitives of one kind (flags == 0), everything else is a 1-object generic run
+    for (int i = 0; i < d.n_objects;) {
+        const rt_prim& p = d.objects[i];
+        const bool plain = p.flags == 0 && p.kind != RT_PRIM_PROGRAM;
+        if (!plain) {
+            if (!s.runs.empty() && s.runs.back().x == rtd::RUN_GENERIC && s.runs.back().y + s.runs.back().z == i) s.runs.back().z++;
+            else s.runs.push_back(make_int4(rtd::RUN_GENERIC, i, 1, 0));
+            ++i; continue;
+        }
+        int j = i; while (j < d.n_objects && d.objects[j].flags == 0 && d.objects[j].kind == p.kind) ++j;
+        const int kind = p.kind == RT_PRIM_SPHERE ? rtd::RUN_SPHERE : p.kind == RT_PRIM_HALFSPACE ? rtd::RUN_HALFSPACE : rtd::RUN_POKEBALL;
+        s.runs.push_back(make_int4(kind, i, j - i, 0));
+        i = j;
+    }
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* rt_version(void) { return "rt_b200 0.1 (sm_100a)"; }
+
+int rt_init(int device) {
+    std::lock_guard<std::mutex> lk(g_ctx.mu);
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail(RT_ERR_CUDA, std::string("no CUDA device: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0") +
+                                     " (this library has no CPU fallback)");
+    if (device < 0) { CU(cudaGetDevice(&device)); }
+    if (g_ctx.ready && g_ctx.device == device) return RT_OK;
+    if (g_ctx.ready) return fail(RT_ERR_STATE, "rt_init: already initialised on another device; call rt_shutdown first");
+    CU(cudaSetDevice(device));
+    cudaDeviceProp prop; CU(cudaGetDeviceProperties(&prop, device));
+    g_ctx.device = device; g_ctx.sms = prop.multiProcessorCount;
+    CU(cudaStreamCreateWithFlags(&g_ctx.stream, cudaStreamNonBlocking));
+    CU(cudaEventCreate(&g_ctx.ev0)); CU(cudaEventCreate(&g_ctx.ev1));
+    CU(cudaMalloc((void**)&g_ctx.counters, 4 * sizeof(unsigned long long)));
+    CU(cudaMalloc((void**)&g_ctx.tile_counter, sizeof(unsigned)));
+    CU(cudaMalloc((void**)&g_ctx.mt_resume, mt::kN * sizeof(uint32_t)));
+    uint32_t seed[mt::kN]; mt::seed_state(12345u, seed);                  // tracer.cpp:284
+    CU(cudaMemcpy(g_ctx.mt_resume, seed, sizeof(seed), cudaMemcpyHostToDevice));
+    g_ctx.mt_tiles = 0; g_ctx.mt_capacity = 0; g_ctx.mt_table = nullptr; g_ctx.const_owner = nullptr;
+    g_ctx.ready = true;
+    return RT_OK;
+}
+
+void rt_shutdown(void) {
+    std::lock_guard<std::mutex> lk(g_ctx.mu);
+    if (!g_ctx.ready) return;
+    cudaSetDevice(g_ctx.device);
+    cudaFree(g_ctx.mt_table); cudaFree(g_ctx.mt_resume); cudaFree(g_ctx.counters); cudaFree(g_ctx.tile_counter);
+    cudaEventDestroy(g_ctx.ev0); cudaEventDestroy(g_ctx.ev1); cudaStreamDestroy(g_ctx.stream);
+    g_ctx.ready = false; g_ctx.device = -1; g_ctx.mt_table = nullptr; g_ctx.mt_tiles = 0; g_ctx.mt_capacity = 0;
+    g_ctx.mt_resume = nullptr; g_ctx.counters = nullptr; g_ctx.tile_counter = nullptr; g_ctx.const_owner = nullptr;
+    g_ctx.stream = nullptr; g_ctx.ev0 = g_ctx.ev1 = nullptr;
+}
+
+int rt_scene_upload(const rt_scene_desc* d, rt_scene** out) {
+    if (!d || !out) return fail(RT_ERR_ARG, "rt_scene_upload: null argument");
+    if (!g_ctx.ready) { int rc = rt_init(-1); if (rc) return rc; }
+    if (d->width <= 0 || d->height <= 0) return fail(RT_ERR_ARG, "rt_scene_upload: empty screen");
+    if (d->recursion > RT_MAX_RECURSION) return fail(RT_ERR_LIMIT, "medium.recursion exceeds RT_MAX_RECURSION");
+    CU(cudaSetDevice(g_ctx.device));
+    auto* s = new rt_scene();
+    build_host_arrays(*d, *s);
+    int rc = RT_OK;
+    if ((rc = upload(s->obj_geom, &s->d_obj_geom)) || (rc = upload(s->obj_meta, &s->d_obj_meta)) ||
+        (rc = upload(s->leaf_geom, &s->d_leaf_geom)) || (rc = upload(s->leaf_meta, &s->d_leaf_meta)) ||
+        (rc = upload(s->pokeballs, &s->d_pokeballs)) || (rc = upload(s->affines, &s->d_affines)) ||
+        (rc = upload(s->ops, &s->d_ops)) || (rc = upload(s->materials, &s->d_materials)) ||
+        (rc = upload(s->lights, &s->d_lights)) || (rc = upload(s->fallbacks, &s->d_fallbacks)) ||
+        (rc = upload(s->runs, &s->d_runs))) { rt_scene_free(s); return rc; }
+    rtd::SceneHeader& h = s->hdr;
+    for (int k = 0; k < 3; ++k) { h.eye[k] = d->eye[k]; h.P[k] = d->screen_p[k]; h.bg[k] = d->background[k]; }
+    h.lx = d->lx; h.ly = d->ly; h.nx = d->width; h.ny = d->height;
+    h.medium_index = d->medium_index; h.recursion = d->recursion;
+    h.n_objects = d->n_objects; h.n_lights = d->n_lights; h.n_runs = (int)s->runs.size();
+    h.obj_geom = s->d_obj_geom; h.obj_meta = s->d_obj_meta; h.leaf_geom = s->d_leaf_geom; h.leaf_meta = s->d_leaf_meta;
+    h.pokeballs = s->d_pokeballs; h.affines = s->d_affines; h.ops = s->d_ops; h.materials = s->d_materials;
+    h.lights = s->d_lights; h.fallbacks = s->d_fallbacks; h.runs = s->d_runs;
+    s->width = d->width; s->height = d->height;
+    s->fits_const = d->n_objects <= rtd::kCObjects && d->n_leaves <= rtd::kCLeaves && d->n_pokeballs <= rtd::kCPokeballs &&
+                    d->n_affines <= rtd::kCAffines && d->n_ops <= rtd::kCOps && d->n_lights <= rtd::kCLights &&
+                    (int)s->runs.size() <= rtd::kCRuns && d->n_fallbacks <= rtd::kCFallbacks;
+    *out = s;
+    return RT_OK;
+}
+
+void rt_scene_free(rt_scene* s) {
+    if (!s) return;
+    if (g_ctx.const_owner == s) g_ctx.const_owner = nullptr;
+    cudaFree(s->d_obj_geom); cudaFree(s->d_obj_meta); cudaFree(s->d_leaf_geom); cudaFree(s->d_leaf_meta);
+    cudaFree(s->d_pokeballs); cudaFree(s->d_affines); cudaFree(s->d_ops); cudaFree(s->d_materials);
+    cudaFree(s->d_lights); cudaFree(s->d_fallbacks); cudaFree(s->d_runs);
+    cudaFree(s->d_rgba8); cudaFree(s->d_rgbf); cudaFree(s->d_ids); cudaFree(s->d_gbuf); cudaFree(s->d_pack);
+    delete s;
+}
+
+int rt_scene_size(const rt_scene* s, int* w, int* h) {
+    if (!s) return fail(RT_ERR_ARG, "rt_scene_size: null scene");
+    if (w) *w = s->width;
+    if (h) *h = s->height;
+    return RT_OK;
+}
+
+}  // extern "C"
+
+namespace {
+
+// Make `s` the scene held in constant memory (header always; arrays when they fit).
+int bind_scene(rt_scene* s, cudaStream_t st) {
+    if (g_ctx.const_owner == s) return RT_OK;
+    CU(cudaMemcpyToSymbolAsync(rtd::c_hdr, &s->hdr, sizeof(s->hdr), 0, cudaMemcpyHostToDevice, st));
+    if (s->fits_const) {
+#define SYM(sym, vec) if (!s->vec.empty()) CU(cudaMemcpyToSymbolAsync(rtd::sym, s->vec.data(), s->vec.size() * sizeof(s->vec[0]), 0, cudaMemcpyHostToDevice, st))
+        SYM(c_obj_geom, obj_geom); SYM(c_obj_meta, obj_meta); SYM(c_leaf_geom, leaf_geom); SYM(c_leaf_meta, leaf_meta);
+        SYM(c_pokeballs, pokeballs); SYM(c_affines, affines); SYM(c_ops, ops); SYM(c_lights, lights);
+        SYM(c_runs, runs); SYM(c_fallbacks, fallbacks);
+#undef SYM
+    }
+    CU(cudaStreamSynchronize(st));      // host vectors are pageable: be done before returning
+    g_ctx.const_owner = s;
+    return RT_OK;
+}
+
+// Extend the jitter checkpoint table to cover `tiles` tiles (scene/resolution independent).
+int ensure_mt_table(long long tiles) {
+    if (tiles <= g_ctx.mt_tiles) return RT_OK;
+    if (tiles > g_ctx.mt_capacity) {
+        long long cap = std::max(tiles, g_ctx.mt_capacity * 2);
+        uint32_t* nt = nullptr;
+        CU(cudaMalloc((void**)&nt, (size_t)cap * mt::kN * sizeof(uint32_t)));
+        if (g_ctx.mt_tiles) CU(cudaMemcpy(nt, g_ctx.mt_table, (size_t)g_ctx.mt_tiles * mt::kN * sizeof(uint32_t), cudaMemcpyDeviceToDevice));
+        cudaFree(g_ctx.mt_table);
+        g_ctx.mt_table = nt; g_ctx.mt_capacity = cap;
+    }
+    rtd::mt_checkpoint_kernel<<<1, 640, 0, g_ctx.stream>>>(g_ctx.mt_table, g_ctx.mt_resume, g_ctx.mt_tiles, tiles - g_ctx.mt_tiles);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(g_ctx.stream));
+    g_ctx.mt_tiles = tiles;
+    return RT_OK;
+}
+
+}  // namespace
+
+namespace {
+
+int ensure_frame_buffers(rt_scene* s, bool want_f, bool want_ids, int mode) {
+    const size_t npx = (size_t)s->width * s->height;
+    if (!s->d_rgba8) CU(cudaMalloc((void**)&s->d_rgba8, npx * sizeof(uchar4)));
+    if (want_f && !s->d_rgbf) CU(cudaMalloc((void**)&s->d_rgbf, npx * sizeof(float4)));
+    const size_t need_ids = npx * (mode == RT_MODE_PAPER ? 1 : 8);
+    if (want_ids && s->ids_elems < need_ids) {
+        cudaFree(s->d_ids); s->d_ids = nullptr;
+        CU(cudaMalloc((void**)&s->d_ids, need_ids * sizeof(int))); s->ids_elems = need_ids;
+    }
+    if (mode == RT_MODE_PAPER && !s->d_gbuf) CU(cudaMalloc((void**)&s->d_gbuf, npx * sizeof(rtd::GBuf)));
+    return RT_OK;
+}
+
+// Launch the frame on `st`.  Counters are reset and read back by the caller.
+int launch_frame(rt_scene* s, int mode, int rank, int world, uchar4* rgba8, float4* rgbf, int* ids, cudaStream_t st, int* n_tiles_out) {
+    const long long npx = (long long)s->width * s->height;
+    int rc = bind_scene(s, st); if (rc) return rc;
+    CU(cudaMemsetAsync(g_ctx.counters, 0, 4 * sizeof(unsigned long long), st));
+    if (mode == RT_MODE_PAPER) {
+        if (!s->d_gbuf) CU(cudaMalloc((void**)&s->d_gbuf, (size_t)npx * sizeof(rtd::GBuf)));
+        const unsigned blocks = (unsigned)((npx + 255) / 256);
+        if (s->fits_const) rtd::paper_gbuffer_kernel<true><<<blocks, 256, 0, st>>>(s->d_gbuf, ids, g_ctx.counters, rank, world);
+        else rtd::paper_gbuffer_kernel<false><<<blocks, 256, 0, st>>>(s->d_gbuf, ids, g_ctx.counters, rank, world);
+        rtd::paper_post_kernel<<<blocks, 256, 0, st>>>(s->d_gbuf, rgba8, rgbf, s->width, s->height, rank, world);
+        CU(cudaGetLastError());
+        if (n_tiles_out) *n_tiles_out = (s->height + rtd::kPaperRows - 1) / rtd::kPaperRows;
+        return RT_OK;
+    }
+    const long long tiles = (npx + mt::kPixelsPerTile - 1) / mt::kPixelsPerTile;
+    rc = ensure_mt_table(tiles); if (rc) return rc;
+    const long long local = tiles > rank ? (tiles - rank + world - 1) / world : 0;
+    rtd::RenderParams prm{};
+    prm.mt_table = g_ctx.mt_table; prm.rgba8 = rgba8; prm.rgbf = rgbf; prm.ids = ids;
+    prm.counters = g_ctx.counters; prm.tile_counter = g_ctx.tile_counter;
+    prm.n_local_tiles = (int)local; prm.rank = rank; prm.world = world; prm.n_pixels = npx;
+    CU(cudaMemsetAsync(g_ctx.tile_counter, 0, sizeof(unsigned), st));
+    int per_sm = 0;
+    if (s->fits_const) CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rtd::render_standard_kernel<true>, rtd::kRenderThreads, 0));
+    else CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rtd::render_standard_kernel<false>, rtd::kRenderThreads, 0));
+    const long long grid = std::max<long long>(1, std::min<long long>(local, (long long)g_ctx.sms * std::max(per_sm, 1)));
+    if (local > 0) {
+        if (s->fits_const) rtd::render_standard_kernel<true><<<(unsigned)grid, rtd::kRenderThreads, 0, st>>>(prm);
+        else rtd::render_standard_kernel<false><<<(unsigned)grid, rtd::kRenderThreads, 0, st>>>(prm);
+        CU(cudaGetLastError());
+    }
+    if (n_tiles_out) *n_tiles_out = (int)local;
+    return RT_OK;
+}
+
+int fill_stats(rt_scene* s, int mode, int n_tiles, float kernel_ms, double total_ms, rt_stats* stats) {
+    if (!stats) return RT_OK;
+    unsigned long long c[4];
+    CU(cudaMemcpy(c, g_ctx.counters, sizeof(c), cudaMemcpyDeviceToHost));
+    stats->kernel_ms = kernel_ms; stats->total_ms = total_ms;
+    stats->primary_rays = c[0]; stats->shadow_rays = c[1]; stats->secondary_rays = c[2]; stats->prim_tests = c[3];
+    stats->width = s->width; stats->height = s->height; stats->samples_per_pixel = mode == RT_MODE_PAPER ? 1 : 8;
+    stats->n_tiles = n_tiles;
+    return RT_OK;
+}
+
+int check_args(rt_scene* s, int mode, int rank, int world) {
+    if (!s) return fail(RT_ERR_ARG, "render: null scene");
+    if (!g_ctx.ready) return fail(RT_ERR_STATE, "render: rt_init has not been called");
+    if (mode != RT_MODE_STANDARD && mode != RT_MODE_PAPER) return fail(RT_ERR_ARG, "render: unknown mode");
+    if (world < 1 || rank < 0 || rank >= world) return fail(RT_ERR_ARG, "render: need 0 <= rank < world");
+    return RT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int rt_render_device(rt_scene* s, int mode, int rank, int world, void* rgba8_device, void* rgbf_device, void* ids_device,
+                     void* stream, rt_stats* stats) {
+    int rc = check_args(s, mode, rank, world); if (rc) return rc;
+    if (!rgba8_device) return fail(RT_ERR_ARG, "rt_render_device: rgba8_device is required");
+    std::lock_guard<std::mutex> lk(g_ctx.mu);
+    CU(cudaSetDevice(g_ctx.device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : g_ctx.stream;
+    const auto t0 = std::chrono::steady_clock::now();
+    int n_tiles = 0;
+    if (mode == RT_MODE_STANDARD) {         // table growth (one-off) must not sit between the events
+        const long long npx = (long long)s->width * s->height;
+        rc = ensure_mt_table((npx + mt::kPixelsPerTile - 1) / mt::kPixelsPerTile); if (rc) return rc;
+    }
+    rc = bind_scene(s, st); if (rc) return rc;
+    CU(cudaEventRecord(g_ctx.ev0, st));
+    rc = launch_frame(s, mode, rank, world, (uchar4*)rgba8_device, (float4*)rgbf_device, (int*)ids_device, st, &n_tiles);
+    if (rc) return rc;
+    CU(cudaEventRecord(g_ctx.ev1, st));
+    if (stats) {
+        CU(cudaEventSynchronize(g_ctx.ev1));
+        float ms = 0.f; CU(cudaEventElapsedTime(&ms, g_ctx.ev0, g_ctx.ev1));
+        const double total = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        return fill_stats(s, mode, n_tiles, ms, total, stats);
+    }
+    return RT_OK;
+}
+
+int rt_render(rt_scene* s, int mode, int rank, int world, uint8_t* rgb8, float* rgbf, int32_t* ids, rt_stats* stats) {
+    int rc = check_args(s, mode, rank, world); if (rc) return rc;
+    std::lock_guard<std::mutex> lk(g_ctx.mu);
+    CU(cudaSetDevice(g_ctx.device));
+    const auto t0 = std::chrono::steady_clock::now();
+    cudaStream_t st = g_ctx.stream;
+    const long long npx = (long long)s->width * s->height;
+    rc = ensure_frame_buffers(s, rgbf != nullptr, ids != nullptr, mode); if (rc) return rc;
+    if (mode == RT_MODE_STANDARD) { rc = ensure_mt_table((npx + mt::kPixelsPerTile - 1) / mt::kPixelsPerTile); if (rc) return rc; }
+    rc = bind_scene(s, st); if (rc) return rc;
+    if (world > 1) {   // pixels of other ranks: defined (zero / -1) so that slices can be summed or compared
+        CU(cudaMemsetAsync(s->d_rgba8, 0, (size_t)npx * sizeof(uchar4), st));
+        if (rgbf) CU(cudaMemsetAsync(s->d_rgbf, 0, (size_t)npx * sizeof(float4), st));
+        if (ids) CU(cudaMemsetAsync(s->d_ids, 0xff, s->ids_elems * sizeof(int), st));
+    }
+    int n_tiles = 0;
+    CU(cudaEventRecord(g_ctx.ev0, st));
+    rc = launch_frame(s, mode, rank, world, s->d_rgba8, rgbf ? s->d_rgbf : nullptr, ids ? s->d_ids : nullptr, st, &n_tiles);
+    if (rc) return rc;
+    CU(cudaEventRecord(g_ctx.ev1, st));
+    const unsigned blocks = (unsigned)((npx + 255) / 256);
+    if (rgb8) {
+        const size_t need = (size_t)npx * 3;
+        if (s->pack_bytes < std::max(need, (size_t)npx * 12)) {
+            cudaFree(s->d_pack); s->d_pack = nullptr;
+            s->pack_bytes = std::max(need, (size_t)npx * 12);
+            CU(cudaMalloc((void**)&s->d_pack, s->pack_bytes));
+        }
+        rtd::pack_rgb_kernel<<<blocks, 256, 0, st>>>(s->d_rgba8, s->d_pack, npx);
+        CU(cudaMemcpyAsync(rgb8, s->d_pack, need, cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+    }
+    if (rgbf) {
+        if (s->pack_bytes < (size_t)npx * 12) {
+            cudaFree(s->d_pack); s->d_pack = nullptr; s->pack_bytes = (size_t)npx * 12;
+            CU(cudaMalloc((void**)&s->d_pack, s->pack_bytes));
+        }
+        rtd::unpack_rgbf_kernel<<<blocks, 256, 0, st>>>(s->d_rgbf, (float*)s->d_pack, npx);
+        CU(cudaMemcpyAsync(rgbf, s->d_pack, (size_t)npx * 12, cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+    }
+    if (ids) CU(cudaMemcpyAsync(ids, s->d_ids, (size_t)npx * (mode == RT_MODE_PAPER ? 1 : 8) * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    CU(cudaGetLastError());
+    float ms = 0.f; CU(cudaEventElapsedTime(&ms, g_ctx.ev0, g_ctx.ev1));
+    const double total = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    return fill_stats(s, mode, n_tiles, ms, total, stats);
+}
+
+int rt_trace_rays(rt_scene* s, int n, const double* rays, double* out) {
+    if (!s || !rays || !out || n < 0) return fail(RT_ERR_ARG, "rt_trace_rays: bad argument");
+    if (!g_ctx.ready) return fail(RT_ERR_STATE, "rt_trace_rays: rt_init has not been called");
+    if (n == 0) return RT_OK;
+    std::lock_guard<std::mutex> lk(g_ctx.mu);
+    CU(cudaSetDevice(g_ctx.device));
+    cudaStream_t st = g_ctx.stream;
+    int rc = bind_scene(s, st); if (rc) return rc;
+    double *d_in = nullptr, *d_out = nullptr;
+    CU(cudaMalloc((void**)&d_in, (size_t)n * 6 * sizeof(double)));
+    CU(cudaMalloc((void**)&d_out, (size_t)n * 16 * sizeof(double)));
+    CU(cudaMemcpyAsync(d_in, rays, (size_t)n * 6 * sizeof(double), cudaMemcpyHostToDevice, st));
+    if (s->fits_const) rtd::trace_rays_kernel<true><<<(n + 127) / 128, 128, 0, st>>>(d_in, d_out, n);
+    else rtd::trace_rays_kernel<false><<<(n + 127) / 128, 128, 0, st>>>(d_in, d_out, n);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out, d_out, (size_t)n * 16 * sizeof(double), cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    cudaFree(d_in); cudaFree(d_out);
+    if (e != cudaSuccess) return fail(RT_ERR_CUDA, std::string("rt_trace_rays: ") + cudaGetErrorString(e));
+    return RT_OK;
+}
+
+int rt_debug_jitter(uint64_t first_sample, int n, double* out) {
+    if (!out || n < 0) return fail(RT_ERR_ARG, "rt_debug_jitter: bad argument");
+    if (!g_ctx.ready) { int rc = rt_init(-1); if (rc) return rc; }
+    if (n == 0) return RT_OK;
+    std::lock_guard<std::mutex> lk(g_ctx.mu);
+    CU(cudaSetDevice(g_ctx.device));
+    const long long tiles = (long long)((first_sample + (uint64_t)n + mt::kSamplesPerTile - 1) / mt::kSamplesPerTile);
+    int rc = ensure_mt_table(tiles); if (rc) return rc;
+    double* d_out = nullptr;
+    CU(cudaMalloc((void**)&d_out, (size_t)n * 2 * sizeof(double)));
+    rtd::jitter_debug_kernel<<<1, 256, 0, g_ctx.stream>>>(g_ctx.mt_table, first_sample, n, d_out);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out, d_out, (size_t)n * 2 * sizeof(double), cudaMemcpyDeviceToHost, g_ctx.stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(g_ctx.stream);
+    cudaFree(d_out);
+    if (e != cudaSuccess) return fail(RT_ERR_CUDA, std::string("rt_debug_jitter: ") + cudaGetErrorString(e));
+    return RT_OK;
+}
+
+int rt_measure_fp32_peak(double* tflops) {
+    if (!tflops) return fail(RT_ERR_ARG, "rt_measure_fp32_peak: null argument");
+    if (!g_ctx.ready) { int rc = rt_init(-1); if (rc) return rc; }
+    std::lock_guard<std::mutex> lk(g_ctx.mu);
+    CU(cudaSetDevice(g_ctx.device));
+    float* sink = nullptr; CU(cudaMalloc((void**)&sink, sizeof(float)));
+    const int iters = 4096, blocks = g_ctx.sms * 8, threads = 256;
+    double best = 0.0;
+    for (int rep = 0; rep < 5; ++rep) {
+        CU(cudaEventRecord(g_ctx.ev0, g_ctx.stream));
+        rtd::ffma_peak_kernel<<<blocks, threads, 0, g_ctx.stream>>>(sink, iters, 1.0000001f, 1e-9f);
+        CU(cudaEventRecord(g_ctx.ev1, g_ctx.stream));
+        CU(cudaEventSynchronize(g_ctx.ev1));
+        float ms = 0.f; CU(cudaEventElapsedTime(&ms, g_ctx.ev0, g_ctx.ev1));
+        const double flops = 2.0 * 8 * 16 * (double)iters * blocks * threads;
+        if (rep > 0) best = std::max(best, flops / (ms * 1e-3) * 1e-12);
+    }
+    cudaFree(sink);
+    *tflops = best;
+    return RT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,359 @@
+// rt_device.cuh — device-side scene layout and ray queries (sm_100a, FP32).
+//
+// Layout in HBM / constant memory:
+//   geom[]  float4 per object/leaf  (sphere: c.xyz, r | half-space: n.xyz, n.p0)
+//   meta[]  int4   per object/leaf  (kind | flags<<8, material, aux, xf)
+// split so that the closest-hit / any-hit scans read 16 B per primitive and touch meta only for
+// the winner.  Small scenes live in __constant__ memory (uniform index -> constant cache /
+// uniform datapath, no LSU traffic); scenes that do not fit use the same arrays in global memory
+// through the read-only path.  `runs` groups consecutive plain primitives of one kind (JSON order
+// is preserved, scene.cpp:15-21) so the scan is a few tight loops instead of a per-object switch.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/rt_b200.h"
+
+namespace rtd {
+
+// ---- capacities of the constant-memory image -------------------------------------------------
+constexpr int kCObjects = 1280, kCLeaves = 256, kCPokeballs = 96, kCAffines = 48, kCOps = 512,
+              kCLights = 32, kCRuns = 192, kCFallbacks = 16;
+
+struct SceneHeader {
+    double eye[3], P[3], lx, ly;
+    int nx, ny;
+    float bg[3]; float medium_index;
+    int recursion, n_objects, n_lights, n_runs;
+    const float4* obj_geom; const int4* obj_meta;
+    const float4* leaf_geom; const int4* leaf_meta;
+    const float4* pokeballs;    // 3 float4 each
+    const float4* affines;      // 3 float4 each (rows)
+    const uint32_t* ops;
+    const float4* materials;    // 3 float4 each: albedo.rgb ks | ambient.rgb kr | kt shininess ior kd
+    const float4* lights;       // 2 float4 each: pos | intensity
+    const float4* fallbacks;
+    const int4* runs;           // kind, first, count, 0
+};
+
+enum { RUN_SPHERE = 0, RUN_HALFSPACE = 1, RUN_POKEBALL = 2, RUN_GENERIC = 3 };
+
+__constant__ SceneHeader c_hdr;
+__constant__ float4 c_obj_geom[kCObjects];
+__constant__ int4   c_obj_meta[kCObjects];
+__constant__ float4 c_leaf_geom[kCLeaves];
+__constant__ int4   c_leaf_meta[kCLeaves];
+__constant__ float4 c_pokeballs[kCPokeballs * 3];
+__constant__ float4 c_affines[kCAffines * 3];
+__constant__ uint32_t c_ops[kCOps];
+__constant__ float4 c_lights[kCLights * 2];
+__constant__ int4   c_runs[kCRuns];
+__constant__ float4 c_fallbacks[kCFallbacks];
+
+// Scene view: C = true reads the constant image, false the global arrays.
+template <bool C> struct SV {
+    static __device__ __forceinline__ float4 obj_geom(int i)  { return C ? c_obj_geom[i]  : __ldg(c_hdr.obj_geom + i); }
+    static __device__ __forceinline__ int4   obj_meta(int i)  { return C ? c_obj_meta[i]  : __ldg(c_hdr.obj_meta + i); }
+    static __device__ __forceinline__ float4 leaf_geom(int i) { return C ? c_leaf_geom[i] : __ldg(c_hdr.leaf_geom + i); }
+    static __device__ __forceinline__ int4   leaf_meta(int i) { return C ? c_leaf_meta[i] : __ldg(c_hdr.leaf_meta + i); }
+    static __device__ __forceinline__ float4 pokeball(int i, int k) { return C ? c_pokeballs[i * 3 + k] : __ldg(c_hdr.pokeballs + i * 3 + k); }
+    static __device__ __forceinline__ float4 affine(int i, int k)   { return C ? c_affines[i * 3 + k]   : __ldg(c_hdr.affines + i * 3 + k); }
+    static __device__ __forceinline__ uint32_t op(int i)      { return C ? c_ops[i]       : __ldg(c_hdr.ops + i); }
+    static __device__ __forceinline__ float4 light(int i, int k)    { return C ? c_lights[i * 2 + k]    : __ldg(c_hdr.lights + i * 2 + k); }
+    static __device__ __forceinline__ int4   run(int i)       { return C ? c_runs[i]      : __ldg(c_hdr.runs + i); }
+    static __device__ __forceinline__ float4 fallback(int i)  { return C ? c_fallbacks[i] : __ldg(c_hdr.fallbacks + i); }
+};
+// materials are indexed per lane (divergent) -> always the global read-only path
+__device__ __forceinline__ float4 material(int m, int k) { return __ldg(c_hdr.materials + m * 3 + k); }
+
+// ---- small vector helpers ---------------------------------------------------------------------
+struct V3 { float x, y, z; };
+__device__ __forceinline__ V3 mk(float x, float y, float z) { V3 v; v.x = x; v.y = y; v.z = z; return v; }
+__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ V3 operator-(V3 a, V3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ V3 operator*(V3 a, float s) { return mk(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ V3 neg(V3 a) { return mk(-a.x, -a.y, -a.z); }
+__device__ __forceinline__ float dot(V3 a, V3 b) { return fmaf(a.x, b.x, fmaf(a.y, b.y, a.z * b.z)); }
+__device__ __forceinline__ V3 madd(V3 a, V3 d, float t) { return mk(fmaf(d.x, t, a.x), fmaf(d.y, t, a.y), fmaf(d.z, t, a.z)); }
+// Vec4::normalized (core.h:58-64): length <= 1e-6 falls back to (0,1,0)
+__device__ __forceinline__ V3 normalized(V3 a) {
+    float l2 = dot(a, a);
+    float L = sqrtf(l2);
+    if (L > 1e-6f) { float inv = 1.0f / L; return mk(a.x * inv, a.y * inv, a.z * inv); }
+    return mk(0.f, 1.f, 0.f);
+}
+
+constexpr float kInf = __builtin_huge_valf();
+
+struct Hit {
+    float t; V3 n; int mat; int code; bool front;
+};
+
+// per-thread ray statistics (rt_stats)
+struct Counters { unsigned primary, shadow, secondary, tests; };
+
+// ---- primitive tests -----------------------------------------------------------------------------
+// Sphere::intersect (geometry.cpp:12-37): near root, else far root, inclusive [tmin,tmax].
+__device__ __forceinline__ bool sphere_t(float4 g, V3 o, V3 d, float tmin, float tmax, float& t) {
+    V3 oc = mk(o.x - g.x, o.y - g.y, o.z - g.z);
+    float hb = dot(oc, d);
+    float cc = fmaf(oc.x, oc.x, fmaf(oc.y, oc.y, fmaf(oc.z, oc.z, -g.w * g.w)));
+    float disc = fmaf(hb, hb, -cc);
+    if (disc < 0.f) return false;
+    float s = sqrtf(disc);
+    float tt = -hb - s;
+    if (tt < tmin || tt > tmax) {
+        tt = -hb + s;
+        if (tt < tmin || tt > tmax) return false;
+    }
+    t = tt;
+    return true;
+}
+// HalfSpace::intersect (geometry.cpp:90-106): g = (n, n.p0)
+__device__ __forceinline__ bool plane_t(float4 g, V3 o, V3 d, float tmin, float tmax, float& t) {
+    float nd = fmaf(g.x, d.x, fmaf(g.y, d.y, g.z * d.z));
+    if (fabsf(nd) < 1e-12f) return false;
+    float no = fmaf(g.x, o.x, fmaf(g.y, o.y, g.z * o.z));
+    float tt = (g.w - no) / nd;
+    if (tt < tmin || tt > tmax) return false;
+    t = tt;
+    return true;
+}
+
+// pick_region_material (geometry.cpp:163-180) on the unit offset u; returns 0..4 = top,bottom,belt,ring,button
+template <bool C> __device__ __forceinline__ int pokeball_region(int pb, V3 u) {
+    float4 a = SV<C>::pokeball(pb, 0), b = SV<C>::pokeball(pb, 1), c = SV<C>::pokeball(pb, 2);
+    float cb = fminf(1.f, fmaxf(-1.f, fmaf(u.x, a.x, fmaf(u.y, a.y, u.z * a.z))));
+    if (cb >= a.w) return (cb <= b.w) ? 3 : 4;
+    float uy = fmaf(u.x, b.x, fmaf(u.y, b.y, u.z * b.z));
+    if (fabsf(uy) <= c.x) return 2;
+    return uy >= 0.f ? 0 : 1;
+}
+
+// world -> leaf-local ray for RT_FLAG_AFFINE leaves (Scaling::intersect, transform.cpp:98-108, composed
+// with the rigid transforms around it).  Returns the stretch L = |A d| (world t = local t / L).
+template <bool C> __device__ __forceinline__ float to_local(int xf, V3 o, V3 d, V3& ol, V3& dl) {
+    float4 r0 = SV<C>::affine(xf, 0), r1 = SV<C>::affine(xf, 1), r2 = SV<C>::affine(xf, 2);
+    ol = mk(fmaf(r0.x, o.x, fmaf(r0.y, o.y, fmaf(r0.z, o.z, r0.w))),
+            fmaf(r1.x, o.x, fmaf(r1.y, o.y, fmaf(r1.z, o.z, r1.w))),
+            fmaf(r2.x, o.x, fmaf(r2.y, o.y, fmaf(r2.z, o.z, r2.w))));
+    V3 dd = mk(fmaf(r0.x, d.x, fmaf(r0.y, d.y, r0.z * d.z)),
+               fmaf(r1.x, d.x, fmaf(r1.y, d.y, r1.z * d.z)),
+               fmaf(r2.x, d.x, fmaf(r2.y, d.y, r2.z * d.z)));
+    float L = sqrtf(dot(dd, dd));
+    if (L > 1e-6f) { float inv = 1.f / L; dl = mk(dd.x * inv, dd.y * inv, dd.z * inv); return L; }
+    dl = mk(0.f, 1.f, 0.f);                  // Ray ctor fallback (core.h:278, 95-101)
+    return 1.f;
+}
+// local normal -> world: n_w = normalize(A^T n_l)  (transform.cpp:117-118 / 201-203 composed)
+template <bool C> __device__ __forceinline__ V3 normal_to_world(int xf, V3 n) {
+    float4 r0 = SV<C>::affine(xf, 0), r1 = SV<C>::affine(xf, 1), r2 = SV<C>::affine(xf, 2);
+    return normalized(mk(fmaf(r0.x, n.x, fmaf(r1.x, n.y, r2.x * n.z)),
+                         fmaf(r0.y, n.x, fmaf(r1.y, n.y, r2.y * n.z)),
+                         fmaf(r0.z, n.x, fmaf(r1.z, n.y, r2.z * n.z))));
+}
+
+// Outward unit normal of a sphere-like leaf at world parameter t, plus the pokeball region.
+template <bool C> __device__ __forceinline__ V3 sphere_outward(float4 g, int4 m, V3 o, V3 d, float t, int& region) {
+    const int flags = (m.x >> 8);
+    V3 out;
+    if (flags & RT_FLAG_AFFINE) {
+        V3 ol, dl; float L = to_local<C>(m.w, o, d, ol, dl);
+        V3 pl = madd(ol, dl, t * L);
+        float ir = 1.f / g.w;
+        V3 ul = mk((pl.x - g.x) * ir, (pl.y - g.y) * ir, (pl.z - g.z) * ir);
+        region = ((m.x & 0xff) == RT_PRIM_POKEBALL) ? pokeball_region<C>(m.z, ul) : 0;
+        // orient in the local frame first (geometry.h:42-45), then map (the orientation commutes)
+        V3 nl = dot(dl, ul) < 0.f ? ul : neg(ul);
+        out = normal_to_world<C>(m.w, nl);
+        return out;
+    }
+    V3 p = madd(o, d, t);
+    float ir = 1.f / g.w;
+    out = mk((p.x - g.x) * ir, (p.y - g.y) * ir, (p.z - g.z) * ir);
+    region = ((m.x & 0xff) == RT_PRIM_POKEBALL) ? pokeball_region<C>(m.z, out) : 0;
+    return out;
+}
+
+// ---- CSG programs (csg.cpp:61-163) ------------------------------------------------------------------
+// An interval end is (t, code): code = leaf | region<<20 | front<<23 | nmode<<24 | fallback<<26,
+// nmode 0 = geometric normal of the leaf at t, 1 = zero normal (csg.cpp:119), 2 = fallbacks[fallback].
+// Normals are evaluated lazily, only for the end that becomes the visible hit.
+struct Ivl { float t0, t1; uint32_t c0, c1; bool ok; };
+constexpr uint32_t kFrontBit = 1u << 23;
+constexpr uint32_t kNModeMask = 3u << 24;
+
+template <bool C> __device__ Ivl leaf_interval(int li, V3 o, V3 d, unsigned& tests) {
+    Ivl r; r.ok = false; r.t0 = 0.f; r.t1 = 0.f; r.c0 = r.c1 = (uint32_t)li;
+    float4 g = SV<C>::leaf_geom(li);
+    int4 m = SV<C>::leaf_meta(li);
+    const int kind = m.x & 0xff, flags = m.x >> 8;
+    ++tests;
+    if (flags & RT_FLAG_NEVER) return r;
+    const bool xformed = flags & RT_FLAG_XFORMED;
+    if (kind == RT_PRIM_HALFSPACE) {                       // HalfSpace::interval (geometry.cpp:117-147)
+        float nd = fmaf(g.x, d.x, fmaf(g.y, d.y, g.z * d.z));
+        float f0 = fmaf(g.x, o.x, fmaf(g.y, o.y, g.z * o.z)) - g.w;
+        if (fabsf(nd) < 1e-12f) {
+            if (!(f0 >= 0.f)) return r;
+            r.t0 = -kInf; r.t1 = kInf;
+        } else {
+            float tp = -f0 / nd;
+            if (nd > 0.f) { r.t0 = tp; r.t1 = kInf; } else { r.t0 = -kInf; r.t1 = tp; }
+        }
+        if (xformed) {                                     // transform.cpp:79-80: ends re-projected from p = ray origin
+            if (!isfinite(r.t0)) r.t0 = 0.f;
+            if (!isfinite(r.t1)) r.t1 = 0.f;
+        }
+        bool front = xformed ? (nd != 0.f) : (nd < 0.f);
+        if (front) { r.c0 |= kFrontBit; r.c1 |= kFrontBit; }
+        r.ok = true;
+        return r;
+    }
+    // Sphere::interval / Pokeball::interval (geometry.cpp:48-78, 207-217)
+    V3 ol = o, dl = d; float L = 1.f;
+    if (flags & RT_FLAG_AFFINE) L = to_local<C>(m.w, o, d, ol, dl);
+    V3 oc = mk(ol.x - g.x, ol.y - g.y, ol.z - g.z);
+    float hb = dot(oc, dl);
+    float cc = fmaf(oc.x, oc.x, fmaf(oc.y, oc.y, fmaf(oc.z, oc.z, -g.w * g.w)));
+    float disc = fmaf(hb, hb, -cc);
+    if (disc < 0.f) return r;
+    float s = sqrtf(disc);
+    float ta = -hb - s, tb = -hb + s;
+    float ir = 1.f / g.w;
+    if (kind == RT_PRIM_POKEBALL) {
+        V3 ua = mk((fmaf(dl.x, ta, ol.x) - g.x) * ir, (fmaf(dl.y, ta, ol.y) - g.y) * ir, (fmaf(dl.z, ta, ol.z) - g.z) * ir);
+        V3 ub = mk((fmaf(dl.x, tb, ol.x) - g.x) * ir, (fmaf(dl.y, tb, ol.y) - g.y) * ir, (fmaf(dl.z, tb, ol.z) - g.z) * ir);
+        r.c0 |= (uint32_t)pokeball_region<C>(m.z, ua) << 20;
+        r.c1 |= (uint32_t)pokeball_region<C>(m.z, ub) << 20;
+    }
+    // front_face = d.outward < 0 with outward = (p - c)/r: at ta it is -s/r, at tb +s/r
+    bool fa = xformed ? (s != 0.f) : (-s * ir < 0.f);
+    bool fb = xformed ? (s != 0.f) : (s * ir < 0.f);
+    if (fa) r.c0 |= kFrontBit;
+    if (fb) r.c1 |= kFrontBit;
+    float iL = 1.f / L;
+    r.t0 = ta * iL; r.t1 = tb * iL;
+    r.ok = true;
+    return r;
+}
+
+__device__ __forceinline__ bool csg_in(int op, bool a, bool b) {
+    return op == RT_CSG_UNION ? (a || b) : op == RT_CSG_INTERSECTION ? (a && b) : (a && !b);
+}
+// event_less (csg.cpp:83-88); k = type | who<<1 (type 0 Enter, 1 Exit; who 0 A, 1 B)
+__device__ __forceinline__ bool ev_less(float ta, int ka, float tb, int kb) {
+    if (fabsf(ta - tb) > 1e-6f) return ta < tb;
+    if ((ka & 1) != (kb & 1)) return (ka & 1) == 0;
+    return (ka >> 1) < (kb >> 1);
+}
+
+// CSG::interval (csg.cpp:61-163) on two child intervals.
+__device__ Ivl csg_combine(int op, const Ivl& A, const Ivl& B) {
+    Ivl R; R.ok = false; R.t0 = 0.f; R.t1 = kInf; R.c0 = R.c1 = 0;
+    if (!A.ok && !B.ok) return R;
+    float et[4]; int ek[4]; int n = 0;
+    // finite ends only (csg.cpp:76-81), initial order A-enter, A-exit, B-enter, B-exit
+    {
+        const float ts[4] = {A.t0, A.t1, B.t0, B.t1};
+        const bool ok[4] = {A.ok, A.ok, B.ok, B.ok};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            bool use = ok[i] && isfinite(ts[i]);
+            // compact without dynamic indexing
+#pragma unroll
+            for (int k = 0; k < 4; ++k) if (use && k == n) { et[k] = ts[i]; ek[k] = i; }
+            n += use ? 1 : 0;
+        }
+    }
+    // libstdc++ insertion sort (std::sort on <= 16 elements), literal: comparator is not a strict weak order
+#pragma unroll
+    for (int i = 1; i < 4; ++i) {
+        if (i < n) {
+            float vt = et[i]; int vk = ek[i];
+            if (ev_less(vt, vk, et[0], ek[0])) {
+#pragma unroll
+                for (int k = i; k > 0; --k) { et[k] = et[k - 1]; ek[k] = ek[k - 1]; }
+                et[0] = vt; ek[0] = vk;
+            } else {
+                bool moving = true;
+#pragma unroll
+                for (int k = i; k > 0; --k) {
+                    if (moving && ev_less(vt, vk, et[k - 1], ek[k - 1])) { et[k] = et[k - 1]; ek[k] = ek[k - 1]; }
+                    else if (moving) { et[k] = vt; ek[k] = vk; moving = false; }
+                }
+                // (the unguarded loop always stops at k >= 1 because !less(val, first))
+            }
+        }
+    }
+    bool inA = A.ok && (A.t0 < 1e-6f) && (A.t1 > 1e-6f);       // csg.cpp:92-96
+    bool inB = B.ok && (B.t0 < 1e-6f) && (B.t1 > 1e-6f);
+    bool inR = csg_in(op, inA, inB);
+    bool haveEnter = false, done = false;
+    float tEnt = 0.f, tExt = kInf; uint32_t cEnt = 0, cExt = 0;
+    if (inR) {                                                 // csg.cpp:114-122: entry at t=0, zero normal, front
+        haveEnter = true;
+        uint32_t src = inA ? A.c0 : B.c0;
+        cEnt = (src & ~(kNModeMask | (63u << 26))) | kFrontBit | (1u << 24);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {                              // csg.cpp:125-156
+        if (i < n && !done) {
+            const int k = ek[i];
+            const bool before = inR;
+            const bool enter = (k & 1) == 0;
+            if ((k >> 1) == 0) inA = enter; else inB = enter;
+            const bool after = csg_in(op, inA, inB);
+            const uint32_t code = k == 0 ? A.c0 : k == 1 ? A.c1 : k == 2 ? B.c0 : B.c1;
+            // A \ B: a boundary contributed by B has its normal negated and re-oriented (csg.cpp:140-142,148-150):
+            // the oriented normal is unchanged, front_face becomes false.
+            if (!before && after) {
+                haveEnter = true; tEnt = et[i];
+                cEnt = (op == RT_CSG_DIFFERENCE && k == 3) ? (code & ~kFrontBit) : code;
+            } else if (before && !after) {
+                tExt = et[i];
+                cExt = (op == RT_CSG_DIFFERENCE && k == 2) ? (code & ~kFrontBit) : code;
+                done = true;
+            }
+            inR = after;
+        }
+    }
+    if (!haveEnter || !isfinite(tExt)) return R;              // csg.cpp:158
+    R.ok = true; R.t0 = tEnt; R.t1 = tExt; R.c0 = cEnt; R.c1 = cExt;
+    return R;
+}
+
+// RT_OP_XFIX: what a transform node does to its child's interval besides moving geometry
+// (transform.cpp:57-86, 140-172, 225-255): ends re-projected from their hit point (non-finite -> 0),
+// zero normals replaced by normalized()'s fallback under Scaling/Rotation, front_face re-derived.
+__device__ __forceinline__ uint32_t xfix_code(uint32_t c, uint32_t arg) {
+    uint32_t nmode = (c >> 24) & 3u;
+    if (nmode == 1u && arg != 0xFFFFFu) { c = (c & ~(kNModeMask | (63u << 26))) | (2u << 24) | (arg << 26); nmode = 2u; }
+    return nmode == 1u ? (c & ~kFrontBit) : (c | kFrontBit);
+}
+__device__ __forceinline__ void xfix(Ivl& v, uint32_t arg) {
+    if (!v.ok) return;
+    if (!isfinite(v.t0)) v.t0 = 0.f;
+    if (!isfinite(v.t1)) v.t1 = 0.f;
+    v.c0 = xfix_code(v.c0, arg);
+    v.c1 = xfix_code(v.c1, arg);
+}
+
+template <bool C> __device__ Ivl run_program(int first, int count, V3 o, V3 d, unsigned& tests) {
+    Ivl acc; acc.ok = false; acc.t0 = acc.t1 = 0.f; acc.c0 = acc.c1 = 0;
+    Ivl stack[RT_MAX_CSG_STACK]; int sp = 0;
+    for (int i = 0; i < count; ++i) {
+        const uint32_t w = SV<C>::op(first + i);
+        const int opcode = w & 15, csg = (w >> 4) & 3; const uint32_t arg = w >> 8;
+        switch (opcode) {
+            case RT_OP_LEAF: acc = leaf_interval<C>((int)arg, o, d, tests); break;
+            case RT_OP_COMBINE_LEAF: { Ivl b = leaf_interval<C>((int)arg, o, d, tests); acc = csg_combine(csg, acc, b); } break;
+            case RT_OP_PUSH: stack[sp++] = acc; break;
+            case RT_OP_COMBINE_POP: { --sp; acc = csg_combine(csg, stack[sp], acc); } break;
+            case RT_OP_XFIX: xfix(acc, arg); break;
+        }
+    }
+    return acc;
+}
+
+}  // namespace rtd

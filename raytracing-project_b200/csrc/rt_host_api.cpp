@@ -1,0 +1,89 @@
+// rt_host_api.cpp — host-only half of the C ABI: error channel, scene compiler entry points
+// (the replacement for jsonio::load_scene_from_json, json_loader.cpp:458-504) and the PNG writer
+// (the replacement for cv::imwrite, main.cpp:84-89; zlib only, no OpenCV).
+#include <zlib.h>
+
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "rt_internal.hpp"
+
+namespace { thread_local std::string g_error; }
+void rt_set_error(const std::string& message) { g_error = message; }
+
+// definition lives in scene_compiler.cpp
+struct rt_compiled;
+namespace rtb { void destroy_compiled(rt_compiled*); const rt_scene_desc* desc_of(const rt_compiled*); }
+
+extern "C" {
+
+const char* rt_last_error(void) { return g_error.c_str(); }
+
+int rt_compile_json_text(const char* json_text, rt_compiled** out) {
+    if (!json_text || !out) { rt_set_error("rt_compile_json_text: null argument"); return RT_ERR_ARG; }
+    *out = nullptr;
+    try {
+        rtb::Scene scene; rtb::Camera cam;
+        jsonio::load_scene_from_json_text(json_text, scene, cam);
+        try { *out = rtb::compile_scene(scene, cam); }
+        catch (const std::exception& e) { rt_set_error(e.what()); return RT_ERR_LIMIT; }
+        return RT_OK;
+    } catch (const std::exception& e) { rt_set_error(e.what()); return RT_ERR_PARSE; }
+}
+
+int rt_compile_json_file(const char* path, rt_compiled** out) {
+    if (!path || !out) { rt_set_error("rt_compile_json_file: null argument"); return RT_ERR_ARG; }
+    *out = nullptr;
+    try {
+        rtb::Scene scene; rtb::Camera cam;
+        jsonio::load_scene_from_json(path, scene, cam);
+        try { *out = rtb::compile_scene(scene, cam); }
+        catch (const std::exception& e) { rt_set_error(e.what()); return RT_ERR_LIMIT; }
+        return RT_OK;
+    } catch (const std::exception& e) {
+        rt_set_error(e.what());
+        return std::strncmp(e.what(), "Cannot open", 11) == 0 ? RT_ERR_IO : RT_ERR_PARSE;
+    }
+}
+
+const rt_scene_desc* rt_compiled_desc(const rt_compiled* c) { return c ? rtb::desc_of(c) : nullptr; }
+void rt_compiled_free(rt_compiled* c) { if (c) rtb::destroy_compiled(c); }
+
+// 8-bit RGB PNG, no alpha, filter 0 on every row, one zlib stream in one IDAT chunk.
+int rt_write_png_rgb8(const char* path, const uint8_t* rgb8, int width, int height) {
+    if (!path || !rgb8 || width <= 0 || height <= 0) { rt_set_error("rt_write_png_rgb8: bad argument"); return RT_ERR_ARG; }
+    const size_t stride = (size_t)width * 3;
+    std::vector<unsigned char> raw((stride + 1) * (size_t)height);
+    for (int y = 0; y < height; ++y) {
+        raw[(stride + 1) * y] = 0;
+        std::memcpy(&raw[(stride + 1) * y + 1], rgb8 + stride * y, stride);
+    }
+    uLongf zlen = compressBound((uLong)raw.size());
+    std::vector<unsigned char> z(zlen);
+    if (compress2(z.data(), &zlen, raw.data(), (uLong)raw.size(), 6) != Z_OK) { rt_set_error("rt_write_png_rgb8: deflate failed"); return RT_ERR_IO; }
+    FILE* f = std::fopen(path, "wb");
+    if (!f) { rt_set_error(std::string("Failed to write PNG: ") + path); return RT_ERR_IO; }
+    auto be32 = [](unsigned char* p, uint32_t v) { p[0] = v >> 24; p[1] = v >> 16; p[2] = v >> 8; p[3] = v; };
+    bool ok = true;
+    auto chunk = [&](const char* type, const unsigned char* data, size_t n) {
+        unsigned char hdr[8]; be32(hdr, (uint32_t)n); std::memcpy(hdr + 4, type, 4);
+        uLong crc = crc32(0L, hdr + 4, 4);
+        if (n) crc = crc32(crc, data, (uInt)n);
+        unsigned char tail[4]; be32(tail, (uint32_t)crc);
+        ok = ok && std::fwrite(hdr, 1, 8, f) == 8 && (n == 0 || std::fwrite(data, 1, n, f) == n) && std::fwrite(tail, 1, 4, f) == 4;
+    };
+    const unsigned char sig[8] = {0x89, 'P', 'N', 'G', 0x0d, 0x0a, 0x1a, 0x0a};
+    ok = std::fwrite(sig, 1, 8, f) == 8;
+    unsigned char ihdr[13]; be32(ihdr, (uint32_t)width); be32(ihdr + 4, (uint32_t)height);
+    ihdr[8] = 8; ihdr[9] = 2; ihdr[10] = 0; ihdr[11] = 0; ihdr[12] = 0;
+    chunk("IHDR", ihdr, 13);
+    chunk("IDAT", z.data(), zlen);
+    chunk("IEND", nullptr, 0);
+    ok = (std::fclose(f) == 0) && ok;
+    if (!ok) { rt_set_error(std::string("Failed to write PNG: ") + path); return RT_ERR_IO; }
+    return RT_OK;
+}
+
+}  // extern "C"

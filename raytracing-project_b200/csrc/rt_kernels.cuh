@@ -1,0 +1,316 @@
+// rt_kernels.cuh — sm_100a kernels of the per-pixel render loop (included once, by rt_api.cu).
+//
+//   mt_checkpoint_kernel   jitter-stream checkpoints (one CTA, sequential twists, parallel inside a twist)
+//   render_standard_kernel Tracer::render Standard (tracer.cpp:282-301): persistent CTAs pull 156-pixel tiles,
+//                          regenerate the tile's 4992 MT19937 outputs in shared memory, trace one sample per
+//                          thread, reduce 8 samples per pixel with shuffles, store float4 / uchar4
+//   paper_gbuffer_kernel + paper_post_kernel   Tracer::render Paper (tracer.cpp:258-281)
+//   trace_rays_kernel      known-answer entry point
+//   ffma_peak_kernel       FP32 roofline denominator
+#pragma once
+#include <cstdio>
+#include "mt19937.cuh"
+#include "rt_trace.cuh"
+
+namespace rtd {
+
+// ---------------------------------------------------------------------------------------------------
+// MT19937 checkpoints: table[j] = state from which tile j's 8 twists start.
+__global__ void __launch_bounds__(640) mt_checkpoint_kernel(uint32_t* table, uint32_t* resume_state, long long first_tile, long long n_tiles) {
+    __shared__ uint32_t st[2][mt::kN];
+    const int k = threadIdx.x;
+    if (k < mt::kN) st[0][k] = resume_state[k];
+    __syncthreads();
+    int cur = 0;
+    for (long long j = 0; j < n_tiles; ++j) {
+        if (k < mt::kN) table[(first_tile + j) * mt::kN + k] = st[cur][k];
+        for (int b = 0; b < mt::kTwistsPerTile; ++b) {
+            if (k < mt::kN) st[cur ^ 1][k] = mt::next_word(st[cur], k);
+            __syncthreads();
+            cur ^= 1;
+        }
+    }
+    if (k < mt::kN) resume_state[k] = st[cur][k];
+}
+
+// First n jitter pairs from sample `first` using the same tile machinery (debug / known-answer).
+__global__ void __launch_bounds__(256) jitter_debug_kernel(const uint32_t* table, unsigned long long first, int n, double* out) {
+    __shared__ uint32_t st[2][mt::kN];
+    __shared__ uint32_t outw[mt::kOutputsPerTile];
+    for (unsigned long long s0 = first; s0 < first + (unsigned long long)n; ) {
+        const unsigned long long tile = s0 / mt::kSamplesPerTile;
+        for (int k = threadIdx.x; k < mt::kN; k += blockDim.x) st[0][k] = table[tile * mt::kN + k];
+        __syncthreads();
+        int cur = 0;
+        for (int b = 0; b < mt::kTwistsPerTile; ++b) {
+            for (int k = threadIdx.x; k < mt::kN; k += blockDim.x) {
+                uint32_t w = mt::next_word(st[cur], k);
+                st[cur ^ 1][k] = w; outw[b * mt::kN + k] = mt::temper(w);
+            }
+            __syncthreads();
+            cur ^= 1;
+        }
+        const unsigned long long tile_first = tile * mt::kSamplesPerTile, tile_end = tile_first + mt::kSamplesPerTile;
+        for (unsigned long long s = s0 + threadIdx.x; s < tile_end && s < first + (unsigned long long)n; s += blockDim.x) {
+            const int j = (int)(s - tile_first);
+            out[2 * (s - first)] = mt::jitter(outw[4 * j], outw[4 * j + 1]);
+            out[2 * (s - first) + 1] = mt::jitter(outw[4 * j + 2], outw[4 * j + 3]);
+        }
+        __syncthreads();
+        s0 = tile_end;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+struct RenderParams {
+    const uint32_t* mt_table;     // checkpoint per tile (standard mode)
+    uchar4* rgba8;                // H*W, row 0 = top
+    float4* rgbf;                 // optional
+    int* ids;                     // optional, H*W*S
+    unsigned long long* counters; // primary, shadow, secondary, tests
+    unsigned* tile_counter;       // dynamic tile scheduler
+    int n_local_tiles, rank, world;
+    long long n_pixels;
+};
+
+__device__ __forceinline__ unsigned char to_byte(float v) {              // toByte (core.h:313-316)
+    float c = fminf(1.f, fmaxf(0.f, v));                                  // NaN -> 1 like std::max(0,std::min(1,v))
+    if (!(v == v)) c = 1.f;
+    return (unsigned char)(int)floorf(c * 255.f + 0.5f);                  // std::round, half away from zero
+}
+
+// Camera::generate_ray_subpixel (camera.h:68-78) in double, rounded to float once.
+__device__ __forceinline__ void camera_ray(double sx, double sy, V3& o, V3& d) {
+    const double Sx = c_hdr.P[0] + c_hdr.lx * sx, Sy = c_hdr.P[1] + c_hdr.ly * sy, Sz = c_hdr.P[2];
+    double dx = Sx - c_hdr.eye[0], dy = Sy - c_hdr.eye[1], dz = Sz - c_hdr.eye[2];
+    const double L = sqrt(dx * dx + dy * dy + dz * dz);
+    if (L > 1e-6) { const double inv = 1.0 / L; dx *= inv; dy *= inv; dz *= inv; } else { dx = 0; dy = 1; dz = 0; }
+    o = mk((float)c_hdr.eye[0], (float)c_hdr.eye[1], (float)c_hdr.eye[2]);
+    d = mk((float)dx, (float)dy, (float)dz);
+}
+
+__device__ __forceinline__ void flush_counters(const Counters& c, unsigned long long* g) {
+    unsigned v[4] = {c.primary, c.shadow, c.secondary, c.tests};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        unsigned x = v[k];
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) x += __shfl_xor_sync(0xffffffffu, x, off);
+        if ((threadIdx.x & 31) == 0 && x) atomicAdd(g + k, (unsigned long long)x);
+    }
+}
+
+constexpr int kRenderThreads = 256;
+
+template <bool C>
+__global__ void __launch_bounds__(kRenderThreads) render_standard_kernel(RenderParams prm) {
+    __shared__ uint32_t st[2][mt::kN];
+    __shared__ __align__(16) uint32_t outw[mt::kOutputsPerTile];
+    __shared__ int s_tile;
+    const int tid = threadIdx.x;
+    const int nx = c_hdr.nx, ny = c_hdr.ny;
+    Counters cnt = {0, 0, 0, 0};
+    for (;;) {
+        if (tid == 0) s_tile = (int)atomicAdd(prm.tile_counter, 1u);
+        __syncthreads();
+        const int local = s_tile;
+        if (local >= prm.n_local_tiles) break;
+        const long long tile = (long long)prm.rank + (long long)local * prm.world;
+        // --- the tile's 4992 raw outputs: checkpoint + 8 twists (one barrier each) ---
+        for (int k = tid; k < mt::kN; k += kRenderThreads) st[0][k] = __ldg(prm.mt_table + tile * mt::kN + k);
+        __syncthreads();
+        int cur = 0;
+#pragma unroll 1
+        for (int b = 0; b < mt::kTwistsPerTile; ++b) {
+            for (int k = tid; k < mt::kN; k += kRenderThreads) {
+                uint32_t w = mt::next_word(st[cur], k);
+                st[cur ^ 1][k] = w; outw[b * mt::kN + k] = mt::temper(w);
+            }
+            __syncthreads();
+            cur ^= 1;
+        }
+        // --- one sample per thread; 8 consecutive lanes share a pixel ---
+        const long long pix0 = tile * mt::kPixelsPerTile;
+#pragma unroll 1
+        for (int pass = 0; pass < (mt::kSamplesPerTile + kRenderThreads - 1) / kRenderThreads; ++pass) {
+            const int j = pass * kRenderThreads + tid;
+            const long long p = pix0 + (j >> 3);
+            const bool active = j < mt::kSamplesPerTile && p < prm.n_pixels;
+            RGBf c = rgb(0.f, 0.f, 0.f);
+            int x = 0, yy = 0;
+            if (active) {
+                const int y = (int)(p / nx); x = (int)(p - (long long)y * nx); yy = ny - 1 - y;   // row flip on store (tracer.cpp:297)
+                const uint4 w = *reinterpret_cast<const uint4*>(outw + 4 * j);
+                const double jx = mt::jitter(w.x, w.y), jy = mt::jitter(w.z, w.w);              // dx first (tracer.cpp:293)
+                const double sx = ((double)x + 0.5 + jx) / (double)nx, sy = ((double)y + 0.5 + jy) / (double)ny;
+                V3 o, d; camera_ray(sx, sy, o, d);
+                Hit ph; bool phit;
+                c = trace<C>(o, d, &ph, &phit, cnt);
+                if (prm.ids) prm.ids[((long long)yy * nx + x) * 8 + (j & 7)] = phit ? ph.code : -1;
+            }
+#pragma unroll
+            for (int off = 1; off < 8; off <<= 1) {
+                c.r += __shfl_xor_sync(0xffffffffu, c.r, off);
+                c.g += __shfl_xor_sync(0xffffffffu, c.g, off);
+                c.b += __shfl_xor_sync(0xffffffffu, c.b, off);
+            }
+            if (active && (j & 7) == 0) {
+                c.r *= 0.125f; c.g *= 0.125f; c.b *= 0.125f;              // acc * (1/spp) (tracer.cpp:296)
+                const long long q = (long long)yy * nx + x;
+                prm.rgba8[q] = make_uchar4(to_byte(c.r), to_byte(c.g), to_byte(c.b), 255);
+                if (prm.rgbf) prm.rgbf[q] = make_float4(c.r, c.g, c.b, 1.f);
+            }
+        }
+        __syncthreads();           // outw / s_tile reuse
+    }
+    flush_counters(cnt, prm.counters);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Paper mode.  The reference re-traces the centre ray and its 4 neighbours for every pixel
+// (tracer.cpp:133-178: 6 closest-hit scans per pixel); a G-buffer removes the 5 redundant ones.
+struct GBuf { float t, nx, ny, nz; int mat; float lum; int code; int hit; };   // 32 B
+
+// rows owned by a rank: blocks of kPaperRows rows, interleaved; halo rows are recomputed locally
+constexpr int kPaperRows = 16;
+__device__ __host__ __forceinline__ bool paper_row_owned(int y, int rank, int world) { return ((y / kPaperRows) % world) == rank; }
+
+template <bool C>
+__global__ void __launch_bounds__(256) paper_gbuffer_kernel(GBuf* gb, int* ids, unsigned long long* counters, int rank, int world) {
+    const int nx = c_hdr.nx, ny = c_hdr.ny;
+    const long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    Counters cnt = {0, 0, 0, 0};
+    if (q < (long long)nx * ny) {
+        const int y = (int)(q / nx), x = (int)(q - (long long)y * nx);
+        const bool own = paper_row_owned(y, rank, world);
+        const bool need = own || (y > 0 && paper_row_owned(y - 1, rank, world)) || (y + 1 < ny && paper_row_owned(y + 1, rank, world));
+        if (need) {
+            // Camera::generate_ray (camera.h:44-58): pixel centre, j flipped
+            const double sx = ((double)x + 0.5) / (double)nx, sy = ((double)(ny - 1 - y) + 0.5) / (double)ny;
+            V3 o, d; camera_ray(sx, sy, o, d);
+            Hit h; GBuf g;
+            ++cnt.primary;
+            const bool hit = closest_hit<C>(o, d, 1e-4f, kInf, h, cnt);      // tracer.cpp:111-120
+            g.hit = hit; g.t = hit ? h.t : kInf; g.mat = hit ? h.mat : -1; g.code = hit ? h.code : -1;
+            g.nx = hit ? h.n.x : 0.f; g.ny = hit ? h.n.y : 0.f; g.nz = hit ? h.n.z : 0.f;
+            RGBf base = rgb(1.f, 1.f, 1.f);
+            if (hit && own) base = shade<C>(h, madd(o, d, h.t), normalized(neg(d)), cnt);
+            g.lum = 0.299f * base.r + 0.587f * base.g + 0.114f * base.b;      // tracer.cpp:123-125
+            gb[q] = g;
+            if (ids && own) ids[q] = g.code;
+        }
+    }
+    flush_counters(cnt, counters);
+}
+
+// apply_crosshatch (tracer.cpp:188-205); C++ % keeps the sign of the dividend, as does CUDA's
+__device__ __forceinline__ float crosshatch(float L, int x, int y) {
+    if (L < 0.15f) return 0.f;
+    const float dark = 1.f - L;
+    const bool d1 = ((x + y) % 4) < 1, d2 = ((x - y) % 4) < 1, hz = (y % 4) < 1;
+    bool line = false;
+    if (dark > 0.8f)       line = (d1 && d2) || hz;
+    else if (dark > 0.65f) line = (d1 && d2) || (hz && ((x + y) % 3 == 0));
+    else if (dark > 0.5f)  line = (d1 && d2) || (hz && ((x + y) % 4 == 0));
+    else if (dark > 0.35f) line = d1 || (hz && ((x + y) % 3 == 0));
+    else if (dark > 0.2f)  line = d1;
+    else if (dark > 0.12f) line = d1 && ((x + y) % 8) < 2;
+    return line ? 0.f : 1.f;
+}
+
+__global__ void __launch_bounds__(256) paper_post_kernel(const GBuf* __restrict__ gb, uchar4* rgba8, float4* rgbf, int nx, int ny, int rank, int world) {
+    const long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= (long long)nx * ny) return;
+    const int y = (int)(q / nx), x = (int)(q - (long long)y * nx);
+    if (!paper_row_owned(y, rank, world)) return;
+    const GBuf c = gb[q];
+    // get_edge_strength (tracer.cpp:133-178)
+    const int dx[4] = {-1, 1, 0, 0}, dy[4] = {0, 0, -1, 1};
+    float edge = 0.f; int valid = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int xn = x + dx[i], yn = y + dy[i];
+        if (xn < 0 || xn >= nx || yn < 0 || yn >= ny) continue;
+        ++valid;
+        const GBuf n = gb[(long long)yn * nx + xn];
+        if ((c.hit != 0) != (n.hit != 0)) { edge = fmaxf(edge, 0.9f); continue; }
+        if (c.hit && n.hit) {
+            const float mn = fminf(c.t, n.t), mx = fmaxf(c.t, n.t);
+            if (mn > 1e-4f && mx / mn > 3.0f) edge = fmaxf(edge, 0.6f);
+            const float nd = fmaf(c.nx, n.nx, fmaf(c.ny, n.ny, c.nz * n.nz));
+            if (nd < 0.2f) edge = fmaxf(edge, 0.5f);
+            if (c.mat != n.mat && nd < 0.7f) edge = fmaxf(edge, 0.3f);
+        }
+    }
+    if (valid < 4) edge *= 0.5f;
+    float v;
+    if (edge > 0.8f) v = 0.f;                                              // tracer.cpp:268-278
+    else if (edge > 0.5f) v = 0.2f;
+    else {
+        v = crosshatch(c.lum, x, y);
+        if (edge > 0.3f) v *= (1.f - (edge - 0.3f) * 0.4f);
+    }
+    const unsigned char b = to_byte(v);
+    rgba8[q] = make_uchar4(b, b, b, 255);                                  // no row flip in paper mode (tracer.cpp:279)
+    if (rgbf) rgbf[q] = make_float4(v, v, v, 1.f);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Known-answer entry point: same record as oracle/ref_driver.cpp --rays.
+template <bool C>
+__global__ void __launch_bounds__(128) trace_rays_kernel(const double* rays, double* out, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double* q = rays + (size_t)i * 6;
+    double dx = q[3], dy = q[4], dz = q[5];
+    const double L = sqrt(dx * dx + dy * dy + dz * dz);
+    if (L > 1e-6) { dx /= L; dy /= L; dz /= L; } else { dx = 0; dy = 1; dz = 0; }
+    const V3 o = mk((float)q[0], (float)q[1], (float)q[2]), d = mk((float)dx, (float)dy, (float)dz);
+    Counters cnt = {0, 0, 0, 0};
+    Hit h; bool hit;
+    const RGBf c = trace<C>(o, d, &h, &hit, cnt);
+    double* r = out + (size_t)i * 16;
+    for (int k = 0; k < 16; ++k) r[k] = 0.0;
+    r[0] = hit ? 1.0 : 0.0;
+    r[1] = hit ? (double)h.t : (double)kInf;
+    if (hit) {
+        const V3 p = madd(o, d, h.t);
+        r[2] = p.x; r[3] = p.y; r[4] = p.z; r[5] = h.n.x; r[6] = h.n.y; r[7] = h.n.z; r[8] = h.front ? 1.0 : 0.0;
+    }
+    r[9] = hit ? (double)h.code : -1.0;
+    r[10] = c.r; r[11] = c.g; r[12] = c.b;
+    r[13] = occluded<C>(o, d, 1e-3f, 5.0f, cnt) ? 1.0 : 0.0;
+    r[14] = (double)cnt.tests; r[15] = (double)(cnt.shadow + cnt.secondary);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// FP32 roofline denominator: 8 independent FFMA chains per thread, no memory traffic.
+__global__ void __launch_bounds__(256) ffma_peak_kernel(float* sink, int iters, float a, float b) {
+    float x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+#pragma unroll 1
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int u = 0; u < 16; ++u) {
+            x0 = fmaf(x0, a, b); x1 = fmaf(x1, a, b); x2 = fmaf(x2, a, b); x3 = fmaf(x3, a, b);
+            x4 = fmaf(x4, a, b); x5 = fmaf(x5, a, b); x6 = fmaf(x6, a, b); x7 = fmaf(x7, a, b);
+        }
+    }
+    const float s = x0 + x1 + x2 + x3 + x4 + x5 + x6 + x7;
+    if (s == 12345.678f) sink[0] = s;
+}
+
+// RGBA8 -> tightly packed RGB8 for the host PNG path
+__global__ void pack_rgb_kernel(const uchar4* __restrict__ in, unsigned char* __restrict__ out, long long n) {
+    const long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= n) return;
+    const uchar4 v = in[q];
+    out[3 * q] = v.x; out[3 * q + 1] = v.y; out[3 * q + 2] = v.z;
+}
+__global__ void unpack_rgbf_kernel(const float4* __restrict__ in, float* __restrict__ out, long long n) {
+    const long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= n) return;
+    const float4 v = in[q];
+    out[3 * q] = v.x; out[3 * q + 1] = v.y; out[3 * q + 2] = v.z;
+}
+
+}  // namespace rtd

@@ -1,0 +1,277 @@
+// rt_trace.cuh — Scene::intersect / Scene::occluded, shade_lambert_phong and the bounded
+// reflection/refraction recursion as device functions (FP32).
+#pragma once
+#include "rt_device.cuh"
+
+namespace rtd {
+
+// ---- generic object (wrapped / affine / program) ---------------------------------------------------
+// Returns true and the hit parameter when object `i` is hit inside the caller's window.  `inclusive`
+// windows are [tmin,tmax] (sphere/plane/pokeball, geometry.cpp:26-28,99), CSG uses t<tmax
+// (csg.cpp:176), transform-wrapped objects tmin<t<tmax (transform.cpp:38).  For programs the entry
+// code and raw entry time are returned for the deferred normal.
+template <bool C>
+__device__ bool generic_hit(int i, V3 o, V3 d, float tmin, float tmax, float& t_out, uint32_t& code_out, float& tent_out, unsigned& tests) {
+    const int4 m = SV<C>::obj_meta(i);
+    const int kind = m.x & 0xff, flags = m.x >> 8;
+    if (flags & RT_FLAG_NEVER) return false;
+    const bool wrapped = flags & RT_FLAG_WRAPPED;
+    const float lo = wrapped ? 0.f : tmin, hi = wrapped ? kInf : tmax;       // transform.cpp:29: child on [0,inf]
+    float t;
+    if (kind == RT_PRIM_PROGRAM) {
+        Ivl v = run_program<C>(m.z, m.w, o, d, tests);
+        if (!v.ok) return false;
+        t = fmaxf(v.t0, lo);                                                 // csg.cpp:175-176
+        if (!(t < v.t1 && t < hi)) return false;
+        code_out = v.c0; tent_out = v.t0;
+    } else {
+        ++tests;
+        const float4 g = SV<C>::obj_geom(i);
+        if (kind == RT_PRIM_HALFSPACE) {
+            if (!plane_t(g, o, d, lo, hi, t)) return false;
+        } else if (flags & RT_FLAG_AFFINE) {
+            V3 ol, dl; float L = to_local<C>(m.w, o, d, ol, dl);
+            float tl;
+            if (!sphere_t(g, ol, dl, lo, hi, tl)) return false;              // local window is [0,inf]: scale-free
+            t = tl / L;
+        } else {
+            if (!sphere_t(g, o, d, lo, hi, t)) return false;
+        }
+        code_out = 0; tent_out = t;
+    }
+    if (wrapped && !(t > tmin && t < tmax)) return false;                    // transform.cpp:38
+    t_out = t;
+    return true;
+}
+
+// ---- Scene::intersect (scene.cpp:10-24) ------------------------------------------------------------------
+template <bool C>
+__device__ bool closest_hit(V3 o, V3 d, float tmin, float tmax, Hit& hit, Counters& cnt) {
+    int best = -1; float best_t = tmax; uint32_t best_code = 0; float best_tent = 0.f;
+    const int n_runs = c_hdr.n_runs;
+    for (int r = 0; r < n_runs; ++r) {
+        const int4 run = SV<C>::run(r);
+        const int first = run.y, end = run.y + run.z;
+        if (run.x == RUN_SPHERE || run.x == RUN_POKEBALL) {
+            cnt.tests += run.z;
+#pragma unroll 4
+            for (int i = first; i < end; ++i) {
+                float t;
+                if (sphere_t(SV<C>::obj_geom(i), o, d, tmin, best_t, t)) { best = i; best_t = t; }
+            }
+        } else if (run.x == RUN_HALFSPACE) {
+            cnt.tests += run.z;
+            for (int i = first; i < end; ++i) {
+                float t;
+                if (plane_t(SV<C>::obj_geom(i), o, d, tmin, best_t, t)) { best = i; best_t = t; }
+            }
+        } else {
+            for (int i = first; i < end; ++i) {
+                float t, tent; uint32_t code;
+                if (generic_hit<C>(i, o, d, tmin, best_t, t, code, tent, cnt.tests)) { best = i; best_t = t; best_code = code; best_tent = tent; }
+            }
+        }
+    }
+    if (best < 0) return false;
+    // ---- finalise the winner: normal, front_face, material, id code ----
+    const int4 m = SV<C>::obj_meta(best);
+    const int kind = m.x & 0xff, flags = m.x >> 8;
+    hit.t = best_t;
+    hit.code = best * 8;
+    V3 outward; bool front; int mat;
+    if (kind == RT_PRIM_PROGRAM) {
+        const uint32_t code = best_code;
+        const int li = code & 0xFFFFF, region = (code >> 20) & 7, nmode = (code >> 24) & 3;
+        const int4 lm = SV<C>::leaf_meta(li);
+        mat = lm.y + region;
+        front = (code & kFrontBit) != 0;
+        V3 n;
+        if (nmode == 1) n = mk(0.f, 0.f, 0.f);                               // csg.cpp:119
+        else {
+            if (nmode == 2) { float4 f = SV<C>::fallback(code >> 26); outward = mk(f.x, f.y, f.z); }
+            else if ((lm.x & 0xff) == RT_PRIM_HALFSPACE) { float4 g = SV<C>::leaf_geom(li); outward = mk(g.x, g.y, g.z); }
+            else { int rg; outward = sphere_outward<C>(SV<C>::leaf_geom(li), lm, o, d, best_tent, rg); }
+            n = dot(d, outward) < 0.f ? outward : neg(outward);              // geometry.h:42-45
+        }
+        if (flags & RT_FLAG_WRAPPED) front = dot(d, n) < 0.f;               // transform.cpp:41
+        hit.n = n; hit.mat = mat; hit.front = front;
+        return true;
+    }
+    const float4 g = SV<C>::obj_geom(best);
+    int region = 0;
+    if (kind == RT_PRIM_HALFSPACE) outward = mk(g.x, g.y, g.z);
+    else outward = sphere_outward<C>(g, m, o, d, best_t, region);
+    front = dot(d, outward) < 0.f;
+    V3 n = front ? outward : neg(outward);
+    if (flags & RT_FLAG_XFORMED) front = dot(d, n) < 0.f;                   // transform.cpp:41
+    mat = m.y;
+    if (kind == RT_PRIM_POKEBALL) { mat += region; hit.code += region + 1; }
+    hit.n = n; hit.mat = mat; hit.front = front;
+    return true;
+}
+
+// ---- Scene::occluded (scene.cpp:33-42) ---------------------------------------------------------------------
+template <bool C>
+__device__ bool occluded(V3 o, V3 d, float tmin, float tmax, Counters& cnt) {
+    const int n_runs = c_hdr.n_runs;
+    for (int r = 0; r < n_runs; ++r) {
+        const int4 run = SV<C>::run(r);
+        const int first = run.y, end = run.y + run.z;
+        if (run.x == RUN_SPHERE || run.x == RUN_POKEBALL) {
+            for (int i = first; i < end; ++i) {
+                float t; ++cnt.tests;
+                if (sphere_t(SV<C>::obj_geom(i), o, d, tmin, tmax, t)) return true;
+            }
+        } else if (run.x == RUN_HALFSPACE) {
+            for (int i = first; i < end; ++i) {
+                float t; ++cnt.tests;
+                if (plane_t(SV<C>::obj_geom(i), o, d, tmin, tmax, t)) return true;
+            }
+        } else {
+            for (int i = first; i < end; ++i) {
+                float t, tent; uint32_t code;
+                if (generic_hit<C>(i, o, d, tmin, tmax, t, code, tent, cnt.tests)) return true;
+            }
+        }
+    }
+    return false;
+}
+
+// ---- shade_lambert_phong (shading.cpp:31-138) ------------------------------------------------------------------
+struct RGBf { float r, g, b; };
+__device__ __forceinline__ RGBf rgb(float r, float g, float b) { RGBf c; c.r = r; c.g = g; c.b = b; return c; }
+// "screen" blend (shading.cpp:6-12)
+__device__ __forceinline__ float screen1(float a, float b) { return 1.f - (1.f - a) * (1.f - b); }
+__device__ __forceinline__ RGBf screen(RGBf a, RGBf b) { return rgb(screen1(a.r, b.r), screen1(a.g, b.g), screen1(a.b, b.b)); }
+
+template <bool C>
+__device__ RGBf shade(const Hit& h, V3 p, V3 wo, Counters& cnt) {
+    if (h.mat < 0) return rgb(1.f, 0.f, 1.f);                                // shading.cpp:33
+    const float4 m0 = material(h.mat, 0), m1 = material(h.mat, 1), m2 = material(h.mat, 2);
+    const float ks = m0.w, shininess = m2.y, kd = m2.w;
+    const V3 n = h.n;
+    RGBf E = rgb(m1.x, m1.y, m1.z);                                          // ambient (x) scene ambient, pre-multiplied
+    const float eps = fmaxf(1e-3f, 1e-4f * h.t);                             // shading.cpp:43
+    const V3 so = madd(p, n, eps);
+    const int nl = c_hdr.n_lights;
+    for (int l = 0; l < nl; ++l) {                                           // shading.cpp:79-130
+        const float4 lp = SV<C>::light(l, 0), li = SV<C>::light(l, 1);
+        V3 L = mk(lp.x - p.x, lp.y - p.y, lp.z - p.z);
+        float d2 = fmaxf(dot(L, L), 0.01f);
+        float dist = sqrtf(d2);
+        float inv = 1.f / dist;
+        V3 wi = mk(L.x * inv, L.y * inv, L.z * inv);
+        float ndotl = fmaxf(0.f, dot(n, wi));
+        if (ndotl <= 0.f) continue;
+        float tmaxS = dist - eps;
+        if (tmaxS <= eps) continue;
+        ++cnt.shadow;
+        if (occluded<C>(so, normalized(wi), eps, tmaxS, cnt)) continue;      // Ray ctor re-normalises (core.h:278)
+        float eff = fmaxf(0.5f, dist);
+        float fall = 2.0f / (eff * eff);                                     // falloff * 2.0 (shading.cpp:108-112)
+        RGBf I = rgb(li.x * fall, li.y * fall, li.z * fall);
+        float kdn = kd * ndotl * 1.5f;                                       // shading.cpp:115
+        RGBf Ed = rgb(m0.x * I.r * kdn, m0.y * I.g * kdn, m0.z * I.b * kdn);
+        RGBf Es = rgb(0.f, 0.f, 0.f);
+        if (ks > 0.f) {                                                      // shading.cpp:118-126
+            float two = 2.f * dot(n, wi);
+            V3 rr = normalized(mk(fmaf(two, n.x, -wi.x), fmaf(two, n.y, -wi.y), fmaf(two, n.z, -wi.z)));
+            float rdotv = fmaxf(0.f, dot(rr, wo));
+            float spec = powf(rdotv, shininess) * ks;
+            Es = rgb(I.r * spec, I.g * spec, I.b * spec);
+        }
+        E = screen(E, screen(Ed, Es));
+    }
+    return rgb(fminf(1.5f, E.r), fminf(1.5f, E.g), fminf(1.5f, E.b));        // shading.cpp:133-135
+}
+
+// ---- Tracer::trace_recursive (tracer.cpp:22-104) as an explicit bounded stack ----------------------------------
+// A node with both kr > 0 and kt > 0 is bilinear in its two children under the screen blend, so the
+// recursion cannot be flattened into a throughput product; each pending node keeps its running `total`
+// and, when a refraction is still owed, the refracted ray.
+struct Frame {
+    RGBf total; float k_pending;    // coefficient of the child currently being traced
+    float kt; V3 ro, rd;            // owed refraction (kt > 0 when owed)
+};
+
+template <bool C>
+__device__ RGBf trace(V3 o, V3 d, Hit* primary, bool* primary_hit, Counters& cnt) {
+    const int limit = c_hdr.recursion;
+    if (primary_hit) *primary_hit = false;
+    if (limit <= 0) {                                                        // tracer.cpp:26 at depth 0
+        if (primary) { Hit h; *primary_hit = closest_hit<C>(o, d, 1e-4f, kInf, h, cnt); *primary = h; }
+        return rgb(0.f, 0.f, 0.f);
+    }
+    Frame stack[RT_MAX_RECURSION];
+    int sp = 0;                     // == depth of the ray being traced
+    RGBf result;
+    for (;;) {
+        // ---- evaluate the ray (o,d) at depth sp ----
+        Hit h;
+        bool hit = closest_hit<C>(o, d, 1e-4f, kInf, h, cnt);                // tracer.cpp:29
+        if (sp == 0) { ++cnt.primary; if (primary) { *primary = h; *primary_hit = hit; } } else ++cnt.secondary;
+        bool descend = false;
+        if (!hit) {
+            result = rgb(c_hdr.bg[0], c_hdr.bg[1], c_hdr.bg[2]);             // tracer.cpp:72
+        } else {
+            const V3 p = madd(o, d, h.t);
+            const V3 wo = normalized(neg(d));
+            RGBf total = shade<C>(h, p, wo, cnt);                            // tracer.cpp:31
+            result = total;
+            if (h.mat >= 0 && sp < limit - 1) {
+                const float4 m1 = material(h.mat, 1), m2 = material(h.mat, 2);
+                const float kr = m1.w, kt = m2.x, ior = m2.z;
+                const V3 I = normalized(d);
+                bool want_r = kr > 0.f, want_t = false;
+                V3 to, td;
+                if (kt > 0.f) {                                              // tracer.cpp:51-68
+                    float eta = h.front ? (c_hdr.medium_index / ior) : (ior / c_hdr.medium_index);
+                    float cos_i = -dot(I, h.n);
+                    float sin_t2 = eta * eta * fmaxf(0.f, 1.f - cos_i * cos_i);
+                    if (!(sin_t2 >= 1.f)) {                                  // TIR guard, tracer.cpp:100-104
+                        float cos_t = sqrtf(1.f - sin_t2);
+                        float kk = eta * cos_i - cos_t;
+                        td = normalized(mk(fmaf(kk, h.n.x, eta * I.x), fmaf(kk, h.n.y, eta * I.y), fmaf(kk, h.n.z, eta * I.z)));
+                        to = h.front ? madd(p, h.n, -1e-6f) : madd(p, h.n, 1e-6f);
+                        want_t = true;
+                    }
+                }
+                if (want_r || want_t) {
+                    Frame& f = stack[sp];
+                    f.total = total;
+                    f.kt = want_t && want_r ? kt : 0.f;
+                    if (want_r) {                                            // tracer.cpp:38-48
+                        float two = 2.f * dot(I, h.n);
+                        V3 rd = normalized(mk(fmaf(-two, h.n.x, I.x), fmaf(-two, h.n.y, I.y), fmaf(-two, h.n.z, I.z)));
+                        V3 ro = h.front ? madd(p, h.n, 1e-6f) : madd(p, h.n, -1e-6f);
+                        f.k_pending = kr;
+                        if (want_t) { f.ro = to; f.rd = td; }
+                        o = ro; d = rd;
+                    } else {
+                        f.k_pending = kt;
+                        o = to; d = td;
+                    }
+                    ++sp;
+                    descend = true;
+                }
+            }
+        }
+        if (descend) continue;
+        // ---- return `result` to the pending parents ----
+        for (;;) {
+            if (sp == 0) return result;
+            Frame& f = stack[sp - 1];
+            const float k = f.k_pending;
+            f.total = screen(f.total, rgb(result.r * k, result.g * k, result.b * k));   // tracer.cpp:47,66
+            if (f.kt > 0.f) {                  // reflection done, refraction owed
+                f.k_pending = f.kt; f.kt = 0.f;
+                o = f.ro; d = f.rd;
+                break;                         // trace it at depth sp (frame stays)
+            }
+            result = f.total;
+            --sp;
+        }
+    }
+}
+
+}  // namespace rtd
