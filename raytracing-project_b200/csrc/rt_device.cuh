@@ -93,12 +93,20 @@ struct Hit {
 struct Counters { unsigned primary, shadow, secondary, tests; };
 
 // ---- primitive tests -----------------------------------------------------------------------------
+// Quadratic of Sphere::intersect (geometry.cpp:15-22) for a unit direction.  The reference evaluates
+// disc = (oc.d)^2 - (oc.oc - r^2) in double; in FP32 that cancels catastrophically once |oc| >> r
+// (an error of 1e-4 in t at |oc| = 17, more than the tracer's tmin).  The same quantity is therefore
+// computed as r^2 - |oc - (oc.d) d|^2, whose rounding error scales with r instead of |oc|.
+__device__ __forceinline__ float sphere_disc(float4 g, V3 o, V3 d, float& hb) {
+    V3 oc = mk(o.x - g.x, o.y - g.y, o.z - g.z);
+    hb = dot(oc, d);
+    V3 l = mk(fmaf(-hb, d.x, oc.x), fmaf(-hb, d.y, oc.y), fmaf(-hb, d.z, oc.z));
+    return fmaf(-l.x, l.x, fmaf(-l.y, l.y, fmaf(-l.z, l.z, g.w * g.w)));
+}
 // Sphere::intersect (geometry.cpp:12-37): near root, else far root, inclusive [tmin,tmax].
 __device__ __forceinline__ bool sphere_t(float4 g, V3 o, V3 d, float tmin, float tmax, float& t) {
-    V3 oc = mk(o.x - g.x, o.y - g.y, o.z - g.z);
-    float hb = dot(oc, d);
-    float cc = fmaf(oc.x, oc.x, fmaf(oc.y, oc.y, fmaf(oc.z, oc.z, -g.w * g.w)));
-    float disc = fmaf(hb, hb, -cc);
+    float hb;
+    float disc = sphere_disc(g, o, d, hb);
     if (disc < 0.f) return false;
     float s = sqrtf(disc);
     float tt = -hb - s;
@@ -213,10 +221,8 @@ template <bool C> __device__ Ivl leaf_interval(int li, V3 o, V3 d, unsigned& tes
     // Sphere::interval / Pokeball::interval (geometry.cpp:48-78, 207-217)
     V3 ol = o, dl = d; float L = 1.f;
     if (flags & RT_FLAG_AFFINE) L = to_local<C>(m.w, o, d, ol, dl);
-    V3 oc = mk(ol.x - g.x, ol.y - g.y, ol.z - g.z);
-    float hb = dot(oc, dl);
-    float cc = fmaf(oc.x, oc.x, fmaf(oc.y, oc.y, fmaf(oc.z, oc.z, -g.w * g.w)));
-    float disc = fmaf(hb, hb, -cc);
+    float hb;
+    float disc = sphere_disc(g, ol, dl, hb);
     if (disc < 0.f) return r;
     float s = sqrtf(disc);
     float ta = -hb - s, tb = -hb + s;

@@ -105,7 +105,7 @@ __device__ bool closest_hit(V3 o, V3 d, float tmin, float tmax, Hit& hit, Counte
     V3 n = front ? outward : neg(outward);
     if (flags & RT_FLAG_XFORMED) front = dot(d, n) < 0.f;                   // transform.cpp:41
     mat = m.y;
-    if (kind == RT_PRIM_POKEBALL) { mat += region; hit.code += region + 1; }
+    if (kind == RT_PRIM_POKEBALL) { mat += region; if (!(flags & RT_FLAG_XFORMED)) hit.code += region + 1; }   // code: only a bare top-level pokeball reports its region
     hit.n = n; hit.mat = mat; hit.front = front;
     return true;
 }
