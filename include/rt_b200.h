@@ -184,6 +184,10 @@ int rt_trace_rays(rt_scene*, int n, const double* rays, double* out);
  * produced by the DEVICE generator; out = 2n doubles (dx, dy).                                   */
 int rt_debug_jitter(uint64_t first_sample, int n, double* out);
 
+/* HOST restatement of the block generator used by the kernels (same inline code, csrc/mt19937.cuh):
+ * the 624 tempered outputs of block `block` (outputs 624*block .. +623) of mt19937(seed).  No GPU needed. */
+int rt_debug_mt_block_host(uint32_t seed, uint64_t block, uint32_t* out624);
+
 /* Measured FP32 FFMA peak of the current device in TFLOP/s (dependent-free FFMA micro-benchmark). */
 int rt_measure_fp32_peak(double* tflops);
 

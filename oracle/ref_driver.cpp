@@ -77,14 +77,14 @@ template <class T> static void put(std::vector<char>& b, const T* p, size_t n) {
 
 static void usage() {
     std::cerr <<
-      "usage: ref_driver <scene.json> [--paper] [--fb out.fb] [--ids out.ids] [--rows y0 y1]\n"
+      "usage: ref_driver <scene.json> [--paper] [--fb out.fb] [--ids out.ids] [--rows y0 y1] [--stride k off]\n"
       "                  [--rays in.rays out.rays] [--quiet] [--repeat n]\n";
 }
 
 int main(int argc, char** argv) {
     if (argc < 2) { usage(); return 1; }
     std::string scene_path = argv[1], fb_path, ids_path, rays_in, rays_out;
-    bool paper = false, quiet = false; int y0 = -1, y1 = -1, repeat = 1;
+    bool paper = false, quiet = false; int y0 = -1, y1 = -1, repeat = 1, stride = 1, stride_off = 0;
     for (int i = 2; i < argc; ++i) {
         std::string a = argv[i];
         if (a == "--paper") paper = true;
@@ -92,6 +92,7 @@ int main(int argc, char** argv) {
         else if (a == "--fb" && i + 1 < argc) fb_path = argv[++i];
         else if (a == "--ids" && i + 1 < argc) ids_path = argv[++i];
         else if (a == "--rows" && i + 2 < argc) { y0 = atoi(argv[++i]); y1 = atoi(argv[++i]); }
+        else if (a == "--stride" && i + 2 < argc) { stride = atoi(argv[++i]); stride_off = atoi(argv[++i]); if (y0 < 0) { y0 = 0; y1 = 1 << 30; } }
         else if (a == "--rays" && i + 2 < argc) { rays_in = argv[++i]; rays_out = argv[++i]; }
         else if (a == "--repeat" && i + 1 < argc) repeat = atoi(argv[++i]);
         else { usage(); return 1; }
@@ -157,11 +158,15 @@ int main(int argc, char** argv) {
         if (y0 < 0) y0 = 0;
         if (y1 > H) y1 = H;
         fb.assign((size_t)W * H, Color{0, 0, 0});
-        auto t0 = std::chrono::steady_clock::now();
+        // --stride k off: only loop rows y with y % k == off (a uniform sample of the frame); skipped rows are
+        // discard()ed from the RNG, and only the time spent inside rendered rows is reported.
         std::mt19937 rng(12345);
         std::uniform_real_distribution<double> uni(-0.5, 0.5);
         rng.discard((unsigned long long)32 * W * y0);
-        for (int y = y0; y < y1; ++y)
+        double ms = 0.0; int rows_done = 0;
+        for (int y = y0; y < y1; ++y) {
+            if (stride > 1 && (y % stride) != stride_off) { rng.discard((unsigned long long)32 * W); continue; }
+            auto t0 = std::chrono::steady_clock::now();
             for (int x = 0; x < W; ++x) {
                 Color acc{0, 0, 0};
                 for (int s = 0; s < 8; ++s) {
@@ -171,8 +176,12 @@ int main(int argc, char** argv) {
                 acc = acc * (1.0 / 8.0);
                 fb[(size_t)(H - 1 - y) * W + x] = acc;
             }
-        auto t1 = std::chrono::steady_clock::now();
-        best_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+            auto t1 = std::chrono::steady_clock::now();
+            ms += std::chrono::duration<double, std::milli>(t1 - t0).count();
+            ++rows_done;
+        }
+        best_ms = ms;
+        std::fprintf(stderr, "rows_rendered %d\n", rows_done);
     }
     if (quiet) std::cout.rdbuf(old);
 

@@ -90,7 +90,7 @@ ABI_SYMBOLS = [
     "rt_init", "rt_shutdown", "rt_last_error", "rt_version",
     "rt_compile_json_text", "rt_compile_json_file", "rt_compiled_desc", "rt_compiled_free",
     "rt_scene_upload", "rt_scene_free", "rt_scene_size",
-    "rt_render", "rt_render_device", "rt_trace_rays", "rt_debug_jitter", "rt_measure_fp32_peak",
+    "rt_render", "rt_render_device", "rt_trace_rays", "rt_debug_jitter", "rt_debug_mt_block_host", "rt_measure_fp32_peak",
     "rt_write_png_rgb8",
 ]
 
@@ -125,6 +125,7 @@ def lib():
                                        C.c_void_p, C.POINTER(RtStats)]
         L.rt_trace_rays.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         L.rt_debug_jitter.argtypes = [C.c_uint64, C.c_int, C.c_void_p]
+        L.rt_debug_mt_block_host.argtypes = [C.c_uint32, C.c_uint64, C.c_void_p]
         L.rt_measure_fp32_peak.argtypes = [C.POINTER(C.c_double)]
         L.rt_write_png_rgb8.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_int]
         _lib = L
@@ -247,6 +248,12 @@ class Tracer:
 def debug_jitter(first_sample: int, n: int) -> np.ndarray:
     out = np.zeros((n, 2), np.float64)
     _check(lib().rt_debug_jitter(first_sample, n, out.ctypes.data_as(C.c_void_p)))
+    return out
+
+
+def mt_block_host(seed: int, block: int) -> np.ndarray:
+    out = np.zeros(624, np.uint32)
+    _check(lib().rt_debug_mt_block_host(seed, block, out.ctypes.data_as(C.c_void_p)))
     return out
 
 

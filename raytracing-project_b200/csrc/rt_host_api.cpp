@@ -9,6 +9,7 @@
 #include <vector>
 
 #include "rt_internal.hpp"
+#include "mt19937.cuh"
 
 namespace { thread_local std::string g_error; }
 void rt_set_error(const std::string& message) { g_error = message; }
@@ -50,6 +51,19 @@ int rt_compile_json_file(const char* path, rt_compiled** out) {
 
 const rt_scene_desc* rt_compiled_desc(const rt_compiled* c) { return c ? rtb::desc_of(c) : nullptr; }
 void rt_compiled_free(rt_compiled* c) { if (c) rtb::destroy_compiled(c); }
+
+int rt_debug_mt_block_host(uint32_t seed, uint64_t block, uint32_t* out624) {
+    if (!out624) { rt_set_error("rt_debug_mt_block_host: null argument"); return RT_ERR_ARG; }
+    uint32_t a[mt::kN], b[mt::kN];
+    mt::seed_state(seed, a);
+    uint32_t *cur = a, *nxt = b;
+    for (uint64_t i = 0; i <= block; ++i) {
+        for (int k = 0; k < mt::kN; ++k) nxt[k] = mt::next_word(cur, k);
+        uint32_t* t = cur; cur = nxt; nxt = t;
+    }
+    for (int k = 0; k < mt::kN; ++k) out624[k] = mt::temper(cur[k]);
+    return RT_OK;
+}
 
 // 8-bit RGB PNG, no alpha, filter 0 on every row, one zlib stream in one IDAT chunk.
 int rt_write_png_rgb8(const char* path, const uint8_t* rgb8, int width, int height) {
