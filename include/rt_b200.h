@@ -96,8 +96,10 @@ typedef struct rt_affine { float m[3][4]; } rt_affine;
  *   RT_OP_XFIX          a transform node sat here: non-finite endpoints -> 0 (transform.cpp:79-80);
  *                       arg != 0xFFFFF: zero normals become fallbacks[arg] (core.h:58-64 via
  *                       transform.cpp:117-118,201-203)
+   RT_OP_COMBINE_SPHERES  a run of COMBINE_LEAF over consecutive plain-sphere leaves, same csg op:
+ *                       arg = first_leaf | count << 14   (first_leaf < 16384, count < 1024)
  * word = opcode | csg_op << 4 | arg << 8                                                           */
-enum { RT_OP_LEAF = 0, RT_OP_COMBINE_LEAF = 1, RT_OP_PUSH = 2, RT_OP_COMBINE_POP = 3, RT_OP_XFIX = 4 };
+enum { RT_OP_LEAF = 0, RT_OP_COMBINE_LEAF = 1, RT_OP_PUSH = 2, RT_OP_COMBINE_POP = 3, RT_OP_XFIX = 4, RT_OP_COMBINE_SPHERES = 5 };
 enum { RT_CSG_UNION = 0, RT_CSG_INTERSECTION = 1, RT_CSG_DIFFERENCE = 2 };
 #define RT_OP_WORD(opcode, csg, arg) ((uint32_t)(opcode) | ((uint32_t)(csg) << 4) | ((uint32_t)(arg) << 8))
 #define RT_MAX_CSG_STACK 8      /* right-nesting depth of a CSG program                   */

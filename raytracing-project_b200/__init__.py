@@ -225,9 +225,14 @@ class Tracer:
             return {"fb": fb, "rgb8": rgb8, "ids": ids}
         return fb
 
-    def render_device(self, rgba8_ptr: int, rgbf_ptr: int = 0, ids_ptr: int = 0, stream: int = 0,
+    def render_device(self, rgba8_ptr: int, rgbf_ptr: int = 0, ids_ptr: int = 0, stream: int | None = None,
                       rank: int = 0, world: int = 1, want_stats: bool = False):
-        """Render into caller-owned DEVICE buffers (e.g. torch tensors' data_ptr()); asynchronous unless want_stats."""
+        """Render into caller-owned DEVICE buffers (e.g. torch tensors' data_ptr()); asynchronous unless want_stats.
+
+        stream: a cudaStream_t as an integer (torch.cuda.current_stream().cuda_stream); 0 means the legacy default
+        stream (passed to the library as cudaStreamLegacy); None means the library's own stream."""
+        if stream is not None and stream == 0:
+            stream = 1          # cudaStreamLegacy: NULL is "library stream" in the C ABI
         st = RtStats()
         _check(lib().rt_render_device(self.scene.device_handle(), int(self.mode), rank, world,
                                       C.c_void_p(rgba8_ptr), C.c_void_p(rgbf_ptr or None), C.c_void_p(ids_ptr or None),

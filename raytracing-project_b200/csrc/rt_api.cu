@@ -29,6 +29,7 @@ struct Context {
     std::mutex mu;
 };
 Context g_ctx;
+constexpr size_t kSceneSmemBudget = 80 * 1024;   // + 25 KB of MT19937 buffers: two CTAs per SM still fit in 227 KB
 
 template <class T> int upload(const std::vector<T>& h, T** d) {
     *d = nullptr;
@@ -42,7 +43,8 @@ template <class T> int upload(const std::vector<T>& h, T** d) {
 
 struct rt_scene {
     rtd::SceneHeader hdr{};
-    bool fits_const{false};
+    bool fits_const{false};   // scanned arrays fit the shared-memory budget (staged per CTA)
+    size_t smem_bytes{0};
     std::vector<float4> obj_geom, leaf_geom, pokeballs, affines, materials, lights, fallbacks;
     std::vector<int4> obj_meta, leaf_meta, runs;
     std::vector<uint32_t> ops;
@@ -134,6 +136,9 @@ int rt_init(int device) {
     uint32_t seed[mt::kN]; mt::seed_state(12345u, seed);                  // tracer.cpp:284
     CU(cudaMemcpy(g_ctx.mt_resume, seed, sizeof(seed), cudaMemcpyHostToDevice));
     g_ctx.mt_tiles = 0; g_ctx.mt_capacity = 0; g_ctx.mt_table = nullptr; g_ctx.const_owner = nullptr;
+    CU(cudaFuncSetAttribute(rtd::render_standard_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget));
+    CU(cudaFuncSetAttribute(rtd::paper_gbuffer_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget));
+    CU(cudaFuncSetAttribute(rtd::trace_rays_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget));
     g_ctx.ready = true;
     return RT_OK;
 }
@@ -173,9 +178,13 @@ int rt_scene_upload(const rt_scene_desc* d, rt_scene** out) {
     h.pokeballs = s->d_pokeballs; h.affines = s->d_affines; h.ops = s->d_ops; h.materials = s->d_materials;
     h.lights = s->d_lights; h.fallbacks = s->d_fallbacks; h.runs = s->d_runs;
     s->width = d->width; s->height = d->height;
-    s->fits_const = d->n_objects <= rtd::kCObjects && d->n_leaves <= rtd::kCLeaves && d->n_pokeballs <= rtd::kCPokeballs &&
-                    d->n_affines <= rtd::kCAffines && d->n_ops <= rtd::kCOps && d->n_lights <= rtd::kCLights &&
-                    (int)s->runs.size() <= rtd::kCRuns && d->n_fallbacks <= rtd::kCFallbacks;
+    h.n_leaves = d->n_leaves; h.n_ops = d->n_ops;
+    h.off_leaf_geom = d->n_objects; h.off_leaf_meta = h.off_leaf_geom + d->n_leaves; h.off_runs = h.off_leaf_meta + d->n_leaves;
+    h.off_lights = h.off_runs + (int)s->runs.size();
+    h.off_ops_bytes = 16 * (h.off_lights + 2 * d->n_lights);
+    h.smem_bytes = h.off_ops_bytes + 4 * d->n_ops;
+    s->smem_bytes = (size_t)h.smem_bytes;
+    s->fits_const = s->smem_bytes <= kSceneSmemBudget;
     *out = s;
     return RT_OK;
 }
@@ -205,13 +214,6 @@ namespace {
 int bind_scene(rt_scene* s, cudaStream_t st) {
     if (g_ctx.const_owner == s) return RT_OK;
     CU(cudaMemcpyToSymbolAsync(rtd::c_hdr, &s->hdr, sizeof(s->hdr), 0, cudaMemcpyHostToDevice, st));
-    if (s->fits_const) {
-#define SYM(sym, vec) if (!s->vec.empty()) CU(cudaMemcpyToSymbolAsync(rtd::sym, s->vec.data(), s->vec.size() * sizeof(s->vec[0]), 0, cudaMemcpyHostToDevice, st))
-        SYM(c_obj_geom, obj_geom); SYM(c_obj_meta, obj_meta); SYM(c_leaf_geom, leaf_geom); SYM(c_leaf_meta, leaf_meta);
-        SYM(c_pokeballs, pokeballs); SYM(c_affines, affines); SYM(c_ops, ops); SYM(c_lights, lights);
-        SYM(c_runs, runs); SYM(c_fallbacks, fallbacks);
-#undef SYM
-    }
     CU(cudaStreamSynchronize(st));      // host vectors are pageable: be done before returning
     g_ctx.const_owner = s;
     return RT_OK;
@@ -260,7 +262,7 @@ int launch_frame(rt_scene* s, int mode, int rank, int world, uchar4* rgba8, floa
     if (mode == RT_MODE_PAPER) {
         if (!s->d_gbuf) CU(cudaMalloc((void**)&s->d_gbuf, (size_t)npx * sizeof(rtd::GBuf)));
         const unsigned blocks = (unsigned)((npx + 255) / 256);
-        if (s->fits_const) rtd::paper_gbuffer_kernel<true><<<blocks, 256, 0, st>>>(s->d_gbuf, ids, g_ctx.counters, rank, world);
+        if (s->fits_const) rtd::paper_gbuffer_kernel<true><<<blocks, 256, s->smem_bytes, st>>>(s->d_gbuf, ids, g_ctx.counters, rank, world);
         else rtd::paper_gbuffer_kernel<false><<<blocks, 256, 0, st>>>(s->d_gbuf, ids, g_ctx.counters, rank, world);
         rtd::paper_post_kernel<<<blocks, 256, 0, st>>>(s->d_gbuf, rgba8, rgbf, s->width, s->height, rank, world);
         CU(cudaGetLastError());
@@ -276,11 +278,11 @@ int launch_frame(rt_scene* s, int mode, int rank, int world, uchar4* rgba8, floa
     prm.n_local_tiles = (int)local; prm.rank = rank; prm.world = world; prm.n_pixels = npx;
     CU(cudaMemsetAsync(g_ctx.tile_counter, 0, sizeof(unsigned), st));
     int per_sm = 0;
-    if (s->fits_const) CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rtd::render_standard_kernel<true>, rtd::kRenderThreads, 0));
+    if (s->fits_const) CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rtd::render_standard_kernel<true>, rtd::kRenderThreads, s->smem_bytes));
     else CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rtd::render_standard_kernel<false>, rtd::kRenderThreads, 0));
     const long long grid = std::max<long long>(1, std::min<long long>(local, (long long)g_ctx.sms * std::max(per_sm, 1)));
     if (local > 0) {
-        if (s->fits_const) rtd::render_standard_kernel<true><<<(unsigned)grid, rtd::kRenderThreads, 0, st>>>(prm);
+        if (s->fits_const) rtd::render_standard_kernel<true><<<(unsigned)grid, rtd::kRenderThreads, s->smem_bytes, st>>>(prm);
         else rtd::render_standard_kernel<false><<<(unsigned)grid, rtd::kRenderThreads, 0, st>>>(prm);
         CU(cudaGetLastError());
     }
@@ -399,7 +401,7 @@ int rt_trace_rays(rt_scene* s, int n, const double* rays, double* out) {
     CU(cudaMalloc((void**)&d_in, (size_t)n * 6 * sizeof(double)));
     CU(cudaMalloc((void**)&d_out, (size_t)n * 16 * sizeof(double)));
     CU(cudaMemcpyAsync(d_in, rays, (size_t)n * 6 * sizeof(double), cudaMemcpyHostToDevice, st));
-    if (s->fits_const) rtd::trace_rays_kernel<true><<<(n + 127) / 128, 128, 0, st>>>(d_in, d_out, n);
+    if (s->fits_const) rtd::trace_rays_kernel<true><<<(n + 127) / 128, 128, s->smem_bytes, st>>>(d_in, d_out, n);
     else rtd::trace_rays_kernel<false><<<(n + 127) / 128, 128, 0, st>>>(d_in, d_out, n);
     cudaError_t e = cudaGetLastError();
     if (e == cudaSuccess) e = cudaMemcpyAsync(out, d_out, (size_t)n * 16 * sizeof(double), cudaMemcpyDeviceToHost, st);

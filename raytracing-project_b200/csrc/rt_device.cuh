@@ -4,9 +4,11 @@
 //   geom[]  float4 per object/leaf  (sphere: c.xyz, r | half-space: n.xyz, n.p0)
 //   meta[]  int4   per object/leaf  (kind | flags<<8, material, aux, xf)
 // split so that the closest-hit / any-hit scans read 16 B per primitive and touch meta only for
-// the winner.  Small scenes live in __constant__ memory (uniform index -> constant cache /
-// uniform datapath, no LSU traffic); scenes that do not fit use the same arrays in global memory
-// through the read-only path.  `runs` groups consecutive plain primitives of one kind (JSON order
+// the winner.  Each CTA stages the scanned arrays into shared memory once (broadcast LDS.128 per
+// primitive per warp); scenes beyond the shared budget use the same arrays through the global
+// read-only path.  (A first version kept them in __constant__ memory: ncu showed every load going
+// through the address-divergence unit, 31 % ADU utilisation, because the scans sit inside divergent
+// per-lane loops where the index is not provably uniform.)  `runs` groups consecutive plain primitives of one kind (JSON order
 // is preserved, scene.cpp:15-21) so the scan is a few tight loops instead of a per-object switch.
 #pragma once
 #include <cuda_runtime.h>
@@ -16,15 +18,13 @@
 
 namespace rtd {
 
-// ---- capacities of the constant-memory image -------------------------------------------------
-constexpr int kCObjects = 1280, kCLeaves = 256, kCPokeballs = 96, kCAffines = 48, kCOps = 512,
-              kCLights = 32, kCRuns = 192, kCFallbacks = 16;
-
 struct SceneHeader {
     double eye[3], P[3], lx, ly;
     int nx, ny;
     float bg[3]; float medium_index;
-    int recursion, n_objects, n_lights, n_runs;
+    int recursion, n_objects, n_lights, n_runs, n_leaves, n_ops;
+    // shared-memory image (units of 16 B from the start of dynamic shared memory; ops in bytes)
+    int off_leaf_geom, off_leaf_meta, off_runs, off_lights, off_ops_bytes, smem_bytes;
     const float4* obj_geom; const int4* obj_meta;
     const float4* leaf_geom; const int4* leaf_meta;
     const float4* pokeballs;    // 3 float4 each
@@ -39,30 +39,41 @@ struct SceneHeader {
 enum { RUN_SPHERE = 0, RUN_HALFSPACE = 1, RUN_POKEBALL = 2, RUN_GENERIC = 3 };
 
 __constant__ SceneHeader c_hdr;
-__constant__ float4 c_obj_geom[kCObjects];
-__constant__ int4   c_obj_meta[kCObjects];
-__constant__ float4 c_leaf_geom[kCLeaves];
-__constant__ int4   c_leaf_meta[kCLeaves];
-__constant__ float4 c_pokeballs[kCPokeballs * 3];
-__constant__ float4 c_affines[kCAffines * 3];
-__constant__ uint32_t c_ops[kCOps];
-__constant__ float4 c_lights[kCLights * 2];
-__constant__ int4   c_runs[kCRuns];
-__constant__ float4 c_fallbacks[kCFallbacks];
+extern __shared__ __align__(16) unsigned char s_scene[];
 
-// Scene view: C = true reads the constant image, false the global arrays.
+// Scene view.  C = true: the arrays every ray scans (object/leaf geometry, leaf meta, CSG ops, runs,
+// lights) were staged into shared memory by stage_scene() — a warp reading one primitive is a single
+// broadcast LDS.128, independent of control-flow divergence.  C = false (scene larger than the shared
+// budget): the same arrays through the global read-only path.  Per-hit data (object meta, pokeball
+// tables, affine maps, materials) is indexed per lane and always comes from global memory.
 template <bool C> struct SV {
-    static __device__ __forceinline__ float4 obj_geom(int i)  { return C ? c_obj_geom[i]  : __ldg(c_hdr.obj_geom + i); }
-    static __device__ __forceinline__ int4   obj_meta(int i)  { return C ? c_obj_meta[i]  : __ldg(c_hdr.obj_meta + i); }
-    static __device__ __forceinline__ float4 leaf_geom(int i) { return C ? c_leaf_geom[i] : __ldg(c_hdr.leaf_geom + i); }
-    static __device__ __forceinline__ int4   leaf_meta(int i) { return C ? c_leaf_meta[i] : __ldg(c_hdr.leaf_meta + i); }
-    static __device__ __forceinline__ float4 pokeball(int i, int k) { return C ? c_pokeballs[i * 3 + k] : __ldg(c_hdr.pokeballs + i * 3 + k); }
-    static __device__ __forceinline__ float4 affine(int i, int k)   { return C ? c_affines[i * 3 + k]   : __ldg(c_hdr.affines + i * 3 + k); }
-    static __device__ __forceinline__ uint32_t op(int i)      { return C ? c_ops[i]       : __ldg(c_hdr.ops + i); }
-    static __device__ __forceinline__ float4 light(int i, int k)    { return C ? c_lights[i * 2 + k]    : __ldg(c_hdr.lights + i * 2 + k); }
-    static __device__ __forceinline__ int4   run(int i)       { return C ? c_runs[i]      : __ldg(c_hdr.runs + i); }
-    static __device__ __forceinline__ float4 fallback(int i)  { return C ? c_fallbacks[i] : __ldg(c_hdr.fallbacks + i); }
+    static __device__ __forceinline__ float4 obj_geom(int i)  { return C ? reinterpret_cast<const float4*>(s_scene)[i] : __ldg(c_hdr.obj_geom + i); }
+    static __device__ __forceinline__ int4   obj_meta(int i)  { return __ldg(c_hdr.obj_meta + i); }
+    static __device__ __forceinline__ float4 leaf_geom(int i) { return C ? reinterpret_cast<const float4*>(s_scene)[c_hdr.off_leaf_geom + i] : __ldg(c_hdr.leaf_geom + i); }
+    static __device__ __forceinline__ int4   leaf_meta(int i) { return C ? reinterpret_cast<const int4*>(s_scene)[c_hdr.off_leaf_meta + i] : __ldg(c_hdr.leaf_meta + i); }
+    static __device__ __forceinline__ float4 pokeball(int i, int k) { return __ldg(c_hdr.pokeballs + i * 3 + k); }
+    static __device__ __forceinline__ float4 affine(int i, int k)   { return __ldg(c_hdr.affines + i * 3 + k); }
+    static __device__ __forceinline__ uint32_t op(int i)      { return C ? reinterpret_cast<const uint32_t*>(s_scene + c_hdr.off_ops_bytes)[i] : __ldg(c_hdr.ops + i); }
+    static __device__ __forceinline__ float4 light(int i, int k)    { return C ? reinterpret_cast<const float4*>(s_scene)[c_hdr.off_lights + i * 2 + k] : __ldg(c_hdr.lights + i * 2 + k); }
+    static __device__ __forceinline__ int4   run(int i)       { return C ? reinterpret_cast<const int4*>(s_scene)[c_hdr.off_runs + i] : __ldg(c_hdr.runs + i); }
+    static __device__ __forceinline__ float4 fallback(int i)  { return __ldg(c_hdr.fallbacks + i); }
 };
+// Copy the scanned arrays into shared memory (all threads of the CTA; ends with a barrier).
+template <bool C> __device__ __forceinline__ void stage_scene() {
+    if (!C) return;
+    float4* dst = reinterpret_cast<float4*>(s_scene);
+    const int t = threadIdx.x, n = blockDim.x;
+    for (int i = t; i < c_hdr.n_objects; i += n) dst[i] = __ldg(c_hdr.obj_geom + i);
+    for (int i = t; i < c_hdr.n_leaves; i += n) {
+        dst[c_hdr.off_leaf_geom + i] = __ldg(c_hdr.leaf_geom + i);
+        reinterpret_cast<int4*>(dst)[c_hdr.off_leaf_meta + i] = __ldg(c_hdr.leaf_meta + i);
+    }
+    for (int i = t; i < c_hdr.n_runs; i += n) reinterpret_cast<int4*>(dst)[c_hdr.off_runs + i] = __ldg(c_hdr.runs + i);
+    for (int i = t; i < 2 * c_hdr.n_lights; i += n) dst[c_hdr.off_lights + i] = __ldg(c_hdr.lights + i);
+    uint32_t* ops = reinterpret_cast<uint32_t*>(s_scene + c_hdr.off_ops_bytes);
+    for (int i = t; i < c_hdr.n_ops; i += n) ops[i] = __ldg(c_hdr.ops + i);
+    __syncthreads();
+}
 // materials are indexed per lane (divergent) -> always the global read-only path
 __device__ __forceinline__ float4 material(int m, int k) { return __ldg(c_hdr.materials + m * 3 + k); }
 
@@ -254,10 +265,30 @@ __device__ __forceinline__ bool ev_less(float ta, int ka, float tb, int kb) {
     return (ka >> 1) < (kb >> 1);
 }
 
+// The synthetic entry CSG::interval records when the combined solid already contains the ray origin
+// (csg.cpp:92-96,114-122): t = 0, zero normal, front_face, material of the child's entry hit.
+__device__ __forceinline__ void origin_rewrite(Ivl& v) {
+    if (v.t0 < 1e-6f && v.t1 > 1e-6f) {
+        v.t0 = 0.f;
+        v.c0 = (v.c0 & ~(kNModeMask | (63u << 26))) | kFrontBit | (1u << 24);
+    }
+}
 // CSG::interval (csg.cpp:61-163) on two child intervals.
 __device__ Ivl csg_combine(int op, const Ivl& A, const Ivl& B) {
     Ivl R; R.ok = false; R.t0 = 0.f; R.t1 = kInf; R.c0 = R.c1 = 0;
     if (!A.ok && !B.ok) return R;
+    if (A.ok != B.ok) {
+        // One child missed.  With a finite, ordered interval X = [t0,t1] of the other child the sweep below
+        // reduces to: Intersection -> empty; Difference with only B -> empty; otherwise X itself, except that
+        // an X containing the ray origin gets the reference's synthetic entry at t=0 (csg.cpp:114-122).
+        const Ivl& X = A.ok ? A : B;
+        if (isfinite(X.t0) && isfinite(X.t1) && X.t0 <= X.t1) {
+            if (op == RT_CSG_INTERSECTION || (op == RT_CSG_DIFFERENCE && !A.ok)) return R;
+            R = X;
+            origin_rewrite(R);
+            return R;
+        }
+    }
     float et[4]; int ek[4]; int n = 0;
     // finite ends only (csg.cpp:76-81), initial order A-enter, A-exit, B-enter, B-exit
     {
@@ -357,6 +388,30 @@ template <bool C> __device__ Ivl run_program(int first, int count, V3 o, V3 d, u
             case RT_OP_PUSH: stack[sp++] = acc; break;
             case RT_OP_COMBINE_POP: { --sp; acc = csg_combine(csg, stack[sp], acc); } break;
             case RT_OP_XFIX: xfix(acc, arg); break;
+            case RT_OP_COMBINE_SPHERES: {            // acc = (...(acc op s[first]) op s[first+1]) ... ) over plain spheres
+                const int first = (int)(arg & 0x3FFFu), n = (int)(arg >> 14);
+                tests += n;
+                for (int k = 0; k < n; ++k) {
+                    const float4 g = SV<C>::leaf_geom(first + k);
+                    float hb;
+                    const float disc = sphere_disc(g, o, d, hb);
+                    if (disc < 0.f) {                 // this sphere is missed: see the one-child case of csg_combine
+                        if (!acc.ok) continue;
+                        if (csg == RT_CSG_INTERSECTION) { acc.ok = false; continue; }
+                        if (isfinite(acc.t0) && isfinite(acc.t1) && acc.t0 <= acc.t1) { origin_rewrite(acc); continue; }
+                        Ivl none; none.ok = false; none.t0 = none.t1 = 0.f; none.c0 = none.c1 = 0;
+                        acc = csg_combine(csg, acc, none);
+                        continue;
+                    }
+                    const float sq = sqrtf(disc), ir = 1.f / g.w;
+                    const bool xformed = (SV<C>::leaf_meta(first + k).x >> 8) & RT_FLAG_XFORMED;
+                    Ivl b; b.ok = true; b.t0 = -hb - sq; b.t1 = -hb + sq;
+                    b.c0 = b.c1 = (uint32_t)(first + k);
+                    if (xformed ? (sq != 0.f) : (-sq * ir < 0.f)) b.c0 |= kFrontBit;
+                    if (xformed ? (sq != 0.f) : (sq * ir < 0.f)) b.c1 |= kFrontBit;
+                    acc = csg_combine(csg, acc, b);
+                }
+            } break;
         }
     }
     return acc;

@@ -110,6 +110,7 @@ __global__ void __launch_bounds__(kRenderThreads) render_standard_kernel(RenderP
     const int tid = threadIdx.x;
     const int nx = c_hdr.nx, ny = c_hdr.ny;
     Counters cnt = {0, 0, 0, 0};
+    stage_scene<C>();
     for (;;) {
         if (tid == 0) s_tile = (int)atomicAdd(prm.tile_counter, 1u);
         __syncthreads();
@@ -180,6 +181,7 @@ __global__ void __launch_bounds__(256) paper_gbuffer_kernel(GBuf* gb, int* ids, 
     const int nx = c_hdr.nx, ny = c_hdr.ny;
     const long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     Counters cnt = {0, 0, 0, 0};
+    stage_scene<C>();
     if (q < (long long)nx * ny) {
         const int y = (int)(q / nx), x = (int)(q - (long long)y * nx);
         const bool own = paper_row_owned(y, rank, world);
@@ -260,6 +262,7 @@ __global__ void __launch_bounds__(256) paper_post_kernel(const GBuf* __restrict_
 template <bool C>
 __global__ void __launch_bounds__(128) trace_rays_kernel(const double* rays, double* out, int n) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    stage_scene<C>();
     if (i >= n) return;
     const double* q = rays + (size_t)i * 6;
     double dx = q[3], dy = q[4], dz = q[5];

@@ -254,6 +254,31 @@ public:
         }
     }
 
+    // Peephole over one object's program: consecutive COMBINE_LEAF ops with the same csg op over consecutive
+    // plain-sphere leaves become one RT_OP_COMBINE_SPHERES (the device runs them as a tight loop).
+    void fuse_sphere_runs(size_t begin) {
+        std::vector<uint32_t> out(ops.begin(), ops.begin() + (long)begin);
+        auto plain_sphere = [&](uint32_t leaf) {
+            const rt_prim& l = leaves[leaf];
+            return l.kind == RT_PRIM_SPHERE && (l.flags & (RT_FLAG_AFFINE | RT_FLAG_NEVER)) == 0;
+        };
+        for (size_t i = begin; i < ops.size();) {
+            const uint32_t w = ops[i];
+            const uint32_t opcode = w & 15u, csg = (w >> 4) & 3u, leaf = w >> 8;
+            if (opcode == RT_OP_COMBINE_LEAF && plain_sphere(leaf)) {
+                size_t j = i + 1;
+                while (j < ops.size() && (ops[j] & 15u) == RT_OP_COMBINE_LEAF && ((ops[j] >> 4) & 3u) == csg &&
+                       (ops[j] >> 8) == leaf + (uint32_t)(j - i) && plain_sphere(ops[j] >> 8) && (j - i) < 1023) ++j;
+                if (j - i >= 2 && leaf < 16384u) {
+                    out.push_back(RT_OP_WORD(RT_OP_COMBINE_SPHERES, csg, leaf | ((uint32_t)(j - i) << 14)));
+                    i = j; continue;
+                }
+            }
+            out.push_back(w); ++i;
+        }
+        ops.swap(out);
+    }
+
     void add_object(const Node& top) {
         Affine M; Ctx ctx;
         const Node* core = &top;
@@ -270,6 +295,7 @@ public:
         p.aux = (int)ops.size();
         int max_depth = 0;
         emit(*core, M, ctx, 0, max_depth);
+        fuse_sphere_runs((size_t)p.aux);
         p.xf = (int)ops.size() - p.aux;
         objects.push_back(p);
     }
