@@ -162,16 +162,16 @@ class Scene:
 
     # -- flat description, for the host-logic tests ---------------------------------------------
     def objects(self):
-        return [self.desc.objects[i] for i in range(self.desc.n_objects)]
+        return [RtPrim.from_buffer_copy(self.desc.objects[i]) for i in range(self.desc.n_objects)]
 
     def leaves(self):
-        return [self.desc.leaves[i] for i in range(self.desc.n_leaves)]
+        return [RtPrim.from_buffer_copy(self.desc.leaves[i]) for i in range(self.desc.n_leaves)]
 
     def ops(self):
         return [int(self.desc.ops[i]) for i in range(self.desc.n_ops)]
 
     def materials(self):
-        return [self.desc.materials[i] for i in range(self.desc.n_materials)]
+        return [RtMaterial.from_buffer_copy(self.desc.materials[i]) for i in range(self.desc.n_materials)]
 
     def device_handle(self):
         if not self._device:

@@ -1,0 +1,56 @@
+"""The oracle (oracle/rt_oracle.cpp) is pinned against the reference itself:
+* committed fixtures produced by the unmodified reference build (tests/golden/make_golden.py) — BIT-EXACT
+  float64 framebuffers, ids, hit distances and per-ray records;
+* where oracle/_ref/ref_driver is present, a live comparison on scene files."""
+import numpy as np
+import pytest
+
+from conftest import golden_names, scene_path
+
+
+@pytest.mark.parametrize("name", golden_names())
+def test_oracle_matches_reference_fixture_standard(oa, goldens, name):
+    g = goldens[name]
+    got = oa.Oracle(g["scene_json"]).render("standard", want_ids=True)
+    assert got["fb"].shape == g["std_fb"].shape
+    assert np.array_equal(got["fb"], g["std_fb"]), "float64 framebuffer differs from the reference's"
+    assert np.array_equal(got["ids"], g["std_ids"])
+    assert np.array_equal(got["t"], g["std_t"])
+
+
+@pytest.mark.parametrize("name", golden_names())
+def test_oracle_matches_reference_fixture_paper(oa, goldens, name):
+    g = goldens[name]
+    got = oa.Oracle(g["scene_json"]).render("paper", want_ids=True)
+    assert np.array_equal(got["fb"], g["paper_fb"])
+    assert np.array_equal(got["ids"], g["paper_ids"])
+    assert np.array_equal(got["t"], g["paper_t"])
+
+
+@pytest.mark.parametrize("name", golden_names())
+def test_oracle_matches_reference_fixture_rays(oa, goldens, name):
+    g = goldens[name]
+    got = oa.Oracle(g["scene_json"]).trace_rays(g["rays"])
+    assert np.array_equal(got[:, :14], g["ray_records"][:, :14])
+    assert g["ray_records"][:, 0].sum() > 20, "fixture should contain hits"
+
+
+def test_oracle_band_equals_full_frame(oa, goldens):
+    """Rows [y0,y1) rendered after discard() reproduce the full-frame stream (the RNG is consumed in pixel order)."""
+    g = goldens["quirks"]
+    o = oa.Oracle(g["scene_json"])
+    H = g["std_fb"].shape[0]
+    band = o.render("standard", rows=(10, 20), threads=1)["fb"]
+    assert np.array_equal(band[H - 20:H - 10], g["std_fb"][H - 20:H - 10])   # loop row y is stored in row H-1-y
+    assert not band[: H - 20].any() and not band[H - 10:].any()
+
+
+@pytest.mark.parametrize("scene,mode", [("pokeballs_small", "standard"), ("quirks", "paper"), ("synthetic_b_small", "standard")])
+def test_oracle_matches_live_reference(oa, scene, mode):
+    if not oa.have_ref():
+        pytest.skip("oracle/_ref/ref_driver not built on this machine")
+    p = scene_path(scene)
+    ref = oa.ref_render(p, mode, want_ids=True)
+    got = oa.Oracle.from_file(p).render(mode, want_ids=True)
+    assert np.array_equal(got["fb"], ref["fb"])
+    assert np.array_equal(got["ids"], ref["ids"])
