@@ -76,7 +76,7 @@ struct RenderParams {
 __device__ __forceinline__ unsigned char to_byte(float v) {              // toByte (core.h:313-316)
     float c = fminf(1.f, fmaxf(0.f, v));                                  // NaN -> 1 like std::max(0,std::min(1,v))
     if (!(v == v)) c = 1.f;
-    return (unsigned char)(int)floorf(c * 255.f + 0.5f);                  // std::round, half away from zero
+    return (unsigned char)(int)floor((double)c * 255.0 + 0.5);           // std::round in double, half away from zero
 }
 
 // Camera::generate_ray_subpixel (camera.h:68-78) in double, rounded to float once.
