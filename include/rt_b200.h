@@ -66,7 +66,9 @@ enum {
  * for the leaves of CSG programs.
  *   sphere / pokeball : geom = cx, cy, cz, r          (Sphere, geometry.h:79-108)
  *   half-space        : geom = nx, ny, nz, n.p0       (HalfSpace, geometry.h:111-158; n unit)
- *   program           : geom unused; aux = first op, xf = op count                              */
+ *   program           : geom = conservative bounding sphere (cx, cy, cz, R) of the program's leaves, or
+ *                       R < 0 when there is none (a half-space or a non-uniformly scaled leaf inside);
+ *                       aux = first op, xf = op count                                            */
 typedef struct rt_prim {
     float   geom[4];
     int32_t kind;     /* RT_PRIM_*                                                     */

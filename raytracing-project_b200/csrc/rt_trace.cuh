@@ -19,6 +19,18 @@ __device__ bool generic_hit(int i, V3 o, V3 d, float tmin, float tmax, float& t_
     const float lo = wrapped ? 0.f : tmin, hi = wrapped ? kInf : tmax;       // transform.cpp:29: child on [0,inf]
     float t;
     if (kind == RT_PRIM_PROGRAM) {
+        // Conservative bounding sphere of the program's leaves (scene compiler; w < 0: none).  A ray whose line
+        // misses it misses every leaf, so CSG::interval fails (csg.cpp:158); if all of it lies behind the
+        // origin or beyond the window the first inside run cannot pass csg.cpp:175-176 / transform.cpp:38.
+        const float4 bs = SV<C>::obj_geom(i);
+        if (bs.w >= 0.f) {
+            ++tests;
+            float hb;
+            const float disc = sphere_disc(bs, o, d, hb);
+            if (disc < 0.f) return false;
+            const float sq = sqrtf(disc);
+            if (-hb + sq < 0.f || -hb - sq > tmax) return false;
+        }
         Ivl v = run_program<C>(m.z, m.w, o, d, tests);
         if (!v.ok) return false;
         t = fmaxf(v.t0, lo);                                                 // csg.cpp:175-176
@@ -54,10 +66,13 @@ __device__ bool closest_hit(V3 o, V3 d, float tmin, float tmax, Hit& hit, Counte
         const int first = run.y, end = run.y + run.z;
         if (run.x == RUN_SPHERE || run.x == RUN_POKEBALL) {
             cnt.tests += run.z;
-#pragma unroll 4
-            for (int i = first; i < end; ++i) {
-                float t;
-                if (sphere_t(SV<C>::obj_geom(i), o, d, tmin, best_t, t)) { best = i; best_t = t; }
+            for (int c0 = first; c0 < end; c0 += 32) {                       // candidates first, finished in JSON order
+                uint32_t mask = sphere_mask<C, false>(c0, min(32, end - c0), o, d);
+                while (mask) {
+                    const int i = c0 + __ffs(mask) - 1; mask &= mask - 1;
+                    float t;
+                    if (sphere_t(SV<C>::obj_geom(i), o, d, tmin, best_t, t)) { best = i; best_t = t; }
+                }
             }
         } else if (run.x == RUN_HALFSPACE) {
             cnt.tests += run.z;
@@ -118,9 +133,15 @@ __device__ bool occluded(V3 o, V3 d, float tmin, float tmax, Counters& cnt) {
         const int4 run = SV<C>::run(r);
         const int first = run.y, end = run.y + run.z;
         if (run.x == RUN_SPHERE || run.x == RUN_POKEBALL) {
-            for (int i = first; i < end; ++i) {
-                float t; ++cnt.tests;
-                if (sphere_t(SV<C>::obj_geom(i), o, d, tmin, tmax, t)) return true;
+            for (int c0 = first; c0 < end; c0 += 32) {                       // any-hit: early-out per chunk of 32
+                const int n = min(32, end - c0);
+                cnt.tests += n;
+                uint32_t mask = sphere_mask<C, false>(c0, n, o, d);
+                while (mask) {
+                    const int i = c0 + __ffs(mask) - 1; mask &= mask - 1;
+                    float t;
+                    if (sphere_t(SV<C>::obj_geom(i), o, d, tmin, tmax, t)) return true;
+                }
             }
         } else if (run.x == RUN_HALFSPACE) {
             for (int i = first; i < end; ++i) {

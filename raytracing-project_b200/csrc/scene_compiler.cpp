@@ -279,6 +279,38 @@ public:
         ops.swap(out);
     }
 
+    // Conservative bounding sphere of a program's leaves (baked to world space), inflated well beyond the FP32
+    // rounding of the device's discriminant, so that "misses the bound" implies "misses every leaf" on the device.
+    // Only when every leaf is a sphere/pokeball in world space; a half-space is unbounded, and a leaf under a
+    // non-uniform scaling is an ellipsoid (left unbounded here).
+    void bound_program(rt_prim& p, size_t leaf0) const {
+        p.geom[0] = p.geom[1] = p.geom[2] = 0.f; p.geom[3] = -1.f;
+        double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+        int n = 0;
+        for (size_t i = leaf0; i < leaves.size(); ++i) {
+            const rt_prim& l = leaves[i];
+            if (l.flags & RT_FLAG_NEVER) continue;
+            if (l.kind == RT_PRIM_HALFSPACE || (l.flags & RT_FLAG_AFFINE)) return;
+            for (int k = 0; k < 3; ++k) {
+                lo[k] = std::min(lo[k], (double)l.geom[k] - std::abs((double)l.geom[3]));
+                hi[k] = std::max(hi[k], (double)l.geom[k] + std::abs((double)l.geom[3]));
+            }
+            ++n;
+        }
+        if (n == 0) return;
+        const double c[3] = {0.5 * (lo[0] + hi[0]), 0.5 * (lo[1] + hi[1]), 0.5 * (lo[2] + hi[2])};
+        double R = 0;
+        for (size_t i = leaf0; i < leaves.size(); ++i) {
+            const rt_prim& l = leaves[i];
+            if (l.flags & RT_FLAG_NEVER) continue;
+            const double dx = l.geom[0] - c[0], dy = l.geom[1] - c[1], dz = l.geom[2] - c[2];
+            R = std::max(R, std::sqrt(dx * dx + dy * dy + dz * dz) + std::abs((double)l.geom[3]));
+        }
+        if (!std::isfinite(R)) return;
+        p.geom[0] = (float)c[0]; p.geom[1] = (float)c[1]; p.geom[2] = (float)c[2];
+        p.geom[3] = (float)(R * 1.002 + 1e-3);
+    }
+
     void add_object(const Node& top) {
         Affine M; Ctx ctx;
         const Node* core = &top;
@@ -294,9 +326,11 @@ public:
         p.flags = (wrapped ? (RT_FLAG_WRAPPED | RT_FLAG_XFORMED) : 0) | (ctx.never ? RT_FLAG_NEVER : 0);
         p.aux = (int)ops.size();
         int max_depth = 0;
+        const size_t leaf0 = leaves.size();
         emit(*core, M, ctx, 0, max_depth);
         fuse_sphere_runs((size_t)p.aux);
         p.xf = (int)ops.size() - p.aux;
+        bound_program(p, leaf0);
         objects.push_back(p);
     }
 };
