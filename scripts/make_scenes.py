@@ -188,6 +188,7 @@ def main() -> None:
     examples()
     dump("synthetic_a_8k.json", synthetic_a(1440))          # 7680x4320, recursion 8
     dump("synthetic_a_small.json", synthetic_a(60))          # 320x180, same scene: full-frame CPU parity
+    dump("synthetic_a_2k.json", synthetic_a(360))           # 1920x1080, same scene: profiling size
     dump("synthetic_a_tiny.json", synthetic_a(45, n_spheres=120, n_pokeballs=16, n_csg=8, recursion=5))  # CPU-test sized
     dump("synthetic_b_16k.json", synthetic_b(4096))         # 16384x16384, recursion 6
     dump("synthetic_b_4k.json", synthetic_b(1024))          # 4096x4096 single-GPU sized
