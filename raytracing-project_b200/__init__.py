@@ -90,7 +90,8 @@ ABI_SYMBOLS = [
     "rt_init", "rt_shutdown", "rt_last_error", "rt_version",
     "rt_compile_json_text", "rt_compile_json_file", "rt_compiled_desc", "rt_compiled_free",
     "rt_scene_upload", "rt_scene_free", "rt_scene_size",
-    "rt_render", "rt_render_device", "rt_trace_rays", "rt_debug_jitter", "rt_debug_mt_block_host", "rt_measure_fp32_peak",
+    "rt_render", "rt_render_device", "rt_trace_rays", "rt_debug_jitter", "rt_debug_mt_block_host", "rt_debug_device_layout",
+    "rt_measure_fp32_peak",
     "rt_write_png_rgb8",
 ]
 
@@ -127,6 +128,7 @@ def lib():
         L.rt_debug_jitter.argtypes = [C.c_uint64, C.c_int, C.c_void_p]
         L.rt_debug_mt_block_host.argtypes = [C.c_uint32, C.c_uint64, C.c_void_p]
         L.rt_measure_fp32_peak.argtypes = [C.POINTER(C.c_double)]
+        L.rt_debug_device_layout.argtypes = [C.POINTER(RtSceneDesc), C.c_void_p, C.POINTER(C.c_int), C.c_void_p, C.POINTER(C.c_int), C.c_void_p]
         L.rt_write_png_rgb8.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_int]
         _lib = L
     return _lib
@@ -172,6 +174,15 @@ class Scene:
 
     def materials(self):
         return [RtMaterial.from_buffer_copy(self.desc.materials[i]) for i in range(self.desc.n_materials)]
+
+    def device_layout(self):
+        """(order, runs[n,4], clusters[m,4]) of the device layout (host-only; see rt_debug_device_layout)."""
+        n = int(self.desc.n_objects)
+        order = np.zeros(max(n, 1), np.int32); runs = np.zeros((max(n, 1), 4), np.int32)
+        clusters = np.zeros((n // 16 + 2, 4), np.float32); nr, nc = C.c_int(), C.c_int()
+        _check(lib().rt_debug_device_layout(C.byref(self.desc), order.ctypes.data_as(C.c_void_p), C.byref(nr),
+                                            runs.ctypes.data_as(C.c_void_p), C.byref(nc), clusters.ctypes.data_as(C.c_void_p)))
+        return order[:n], runs[: nr.value], clusters[: nc.value]
 
     def device_handle(self):
         if not self._device:

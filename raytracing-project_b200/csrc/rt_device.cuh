@@ -22,9 +22,9 @@ struct SceneHeader {
     double eye[3], P[3], lx, ly;
     int nx, ny;
     float bg[3]; float medium_index;
-    int recursion, n_objects, n_lights, n_runs, n_leaves, n_ops;
+    int recursion, n_objects, n_lights, n_runs, n_leaves, n_ops, n_clusters;
     // shared-memory image (units of 16 B from the start of dynamic shared memory; ops in bytes)
-    int off_leaf_geom, off_leaf_meta, off_runs, off_lights, off_ops_bytes, smem_bytes;
+    int off_leaf_geom, off_leaf_meta, off_runs, off_lights, off_clusters, off_ops_bytes, smem_bytes;
     const float4* obj_geom; const int4* obj_meta;
     const float4* leaf_geom; const int4* leaf_meta;
     const float4* pokeballs;    // 3 float4 each
@@ -33,7 +33,9 @@ struct SceneHeader {
     const float4* materials;    // 3 float4 each: albedo.rgb ks | ambient.rgb kr | kt shininess ior kd
     const float4* lights;       // 2 float4 each: pos | intensity
     const float4* fallbacks;
-    const int4* runs;           // kind, first, count, 0
+    const int4* runs;           // kind, first, count, 1 + first cluster (0: run is not clustered)
+    const float4* clusters;     // bounding sphere of every 16 consecutive primitives of a clustered run
+    const int* obj_orig;        // JSON index of device object i (clustered runs are reordered spatially)
 };
 
 enum { RUN_SPHERE = 0, RUN_HALFSPACE = 1, RUN_POKEBALL = 2, RUN_GENERIC = 3 };
@@ -57,6 +59,12 @@ template <bool C> struct SV {
     static __device__ __forceinline__ float4 light(int i, int k)    { return C ? reinterpret_cast<const float4*>(s_scene)[c_hdr.off_lights + i * 2 + k] : __ldg(c_hdr.lights + i * 2 + k); }
     static __device__ __forceinline__ int4   run(int i)       { return C ? reinterpret_cast<const int4*>(s_scene)[c_hdr.off_runs + i] : __ldg(c_hdr.runs + i); }
     static __device__ __forceinline__ float4 fallback(int i)  { return __ldg(c_hdr.fallbacks + i); }
+    static __device__ __forceinline__ float4 cluster(int i)   { return C ? reinterpret_cast<const float4*>(s_scene)[c_hdr.off_clusters + i] : __ldg(c_hdr.clusters + i); }
+    static __device__ __forceinline__ int    obj_orig(int i)  { return __ldg(c_hdr.obj_orig + i); }
+    // base pointers for sphere_mask
+    static __device__ __forceinline__ const float4* obj_ptr(int i)     { return C ? reinterpret_cast<const float4*>(s_scene) + i : c_hdr.obj_geom + i; }
+    static __device__ __forceinline__ const float4* leaf_ptr(int i)    { return C ? reinterpret_cast<const float4*>(s_scene) + c_hdr.off_leaf_geom + i : c_hdr.leaf_geom + i; }
+    static __device__ __forceinline__ const float4* cluster_ptr(int i) { return C ? reinterpret_cast<const float4*>(s_scene) + c_hdr.off_clusters + i : c_hdr.clusters + i; }
 };
 // Copy the scanned arrays into shared memory (all threads of the CTA; ends with a barrier).
 template <bool C> __device__ __forceinline__ void stage_scene() {
@@ -70,6 +78,7 @@ template <bool C> __device__ __forceinline__ void stage_scene() {
     }
     for (int i = t; i < c_hdr.n_runs; i += n) reinterpret_cast<int4*>(dst)[c_hdr.off_runs + i] = __ldg(c_hdr.runs + i);
     for (int i = t; i < 2 * c_hdr.n_lights; i += n) dst[c_hdr.off_lights + i] = __ldg(c_hdr.lights + i);
+    for (int i = t; i < c_hdr.n_clusters; i += n) dst[c_hdr.off_clusters + i] = __ldg(c_hdr.clusters + i);
     uint32_t* ops = reinterpret_cast<uint32_t*>(s_scene + c_hdr.off_ops_bytes);
     for (int i = t; i < c_hdr.n_ops; i += n) ops[i] = __ldg(c_hdr.ops + i);
     __syncthreads();
@@ -145,9 +154,7 @@ __device__ __forceinline__ bool plane_t(float4 g, V3 o, V3 d, float tmin, float 
 // primitive, no data-dependent branch, four independent chains in flight.  The (rare) candidates are then
 // finished in order by the caller with exactly the arithmetic of sphere_t / leaf_interval, so the result is
 // bit-identical to testing the primitives one after the other.   cnt <= 32.
-template <bool C, bool LEAF> __device__ __forceinline__ uint32_t sphere_mask(int first, int cnt, V3 o, V3 d) {
-    const float4* base = C ? reinterpret_cast<const float4*>(s_scene) + (LEAF ? c_hdr.off_leaf_geom : 0) + first
-                           : (LEAF ? c_hdr.leaf_geom : c_hdr.obj_geom) + first;
+template <bool C> __device__ __forceinline__ uint32_t sphere_mask(const float4* base, int cnt, V3 o, V3 d) {
     uint32_t mask = 0;
     int k = 0;
     for (; k + 4 <= cnt; k += 4) {
@@ -422,7 +429,7 @@ template <bool C> __device__ Ivl run_program(int first, int count, V3 o, V3 d, u
                 tests += n;
                 for (int c0 = 0; c0 < n; c0 += 32) {
                     const int cnt = min(32, n - c0), base = first + c0;
-                    uint32_t mask = sphere_mask<C, true>(base, cnt, o, d);
+                    uint32_t mask = sphere_mask<C>(SV<C>::leaf_ptr(base), cnt, o, d);
                     int pos = 0;
                     for (;;) {
                         const int k = mask ? (__ffs(mask) - 1) : cnt;          // next candidate, or the end of the chunk

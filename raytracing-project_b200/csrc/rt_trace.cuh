@@ -57,17 +57,43 @@ __device__ bool generic_hit(int i, V3 o, V3 d, float tmin, float tmax, float& t_
 }
 
 // ---- Scene::intersect (scene.cpp:10-24) ------------------------------------------------------------------
-template <bool C>
+template <bool C, bool K>
 __device__ bool closest_hit(V3 o, V3 d, float tmin, float tmax, Hit& hit, Counters& cnt) {
     int best = -1; float best_t = tmax; uint32_t best_code = 0; float best_tent = 0.f;
     const int n_runs = c_hdr.n_runs;
     for (int r = 0; r < n_runs; ++r) {
         const int4 run = SV<C>::run(r);
         const int first = run.y, end = run.y + run.z;
-        if (run.x == RUN_SPHERE || run.x == RUN_POKEBALL) {
+        if (K && (run.x == RUN_SPHERE || run.x == RUN_POKEBALL) && run.w > 0) {
+            // Clustered run (spatially reordered, 16 primitives per cluster): candidate mask over the cluster bounds,
+            // then over the members of the clusters whose bound overlaps the window.  A sphere's candidate root does
+            // not depend on the order of the scan; exact ties go to the later JSON index as in scene.cpp:15-21.
+            const int ctab = run.w - 1, ncl = (run.z + 15) >> 4;
+            cnt.tests += ncl;
+            for (int cb = 0; cb < ncl; cb += 32) {
+                uint32_t cmask = sphere_mask<C>(SV<C>::cluster_ptr(ctab + cb), min(32, ncl - cb), o, d);
+                while (cmask) {
+                    const int c = cb + __ffs(cmask) - 1; cmask &= cmask - 1;
+                    float hb;
+                    const float disc = sphere_disc(SV<C>::cluster(ctab + c), o, d, hb);
+                    const float sq = sqrtf(disc);
+                    if (-hb + sq < 0.f || -hb - sq > best_t) continue;
+                    const int m0 = first + 16 * c, n = min(16, end - m0);
+                    cnt.tests += n;
+                    uint32_t mask = sphere_mask<C>(SV<C>::obj_ptr(m0), n, o, d);
+                    while (mask) {
+                        const int i = m0 + __ffs(mask) - 1; mask &= mask - 1;
+                        float t;
+                        if (!sphere_t(SV<C>::obj_geom(i), o, d, tmin, best_t, t)) continue;
+                        if (t == best_t && best >= 0 && SV<C>::obj_orig(i) < SV<C>::obj_orig(best)) continue;
+                        best = i; best_t = t;
+                    }
+                }
+            }
+        } else if (run.x == RUN_SPHERE || run.x == RUN_POKEBALL) {
             cnt.tests += run.z;
             for (int c0 = first; c0 < end; c0 += 32) {                       // candidates first, finished in JSON order
-                uint32_t mask = sphere_mask<C, false>(c0, min(32, end - c0), o, d);
+                uint32_t mask = sphere_mask<C>(SV<C>::obj_ptr(c0), min(32, end - c0), o, d);
                 while (mask) {
                     const int i = c0 + __ffs(mask) - 1; mask &= mask - 1;
                     float t;
@@ -92,7 +118,7 @@ __device__ bool closest_hit(V3 o, V3 d, float tmin, float tmax, Hit& hit, Counte
     const int4 m = SV<C>::obj_meta(best);
     const int kind = m.x & 0xff, flags = m.x >> 8;
     hit.t = best_t;
-    hit.code = best * 8;
+    hit.code = SV<C>::obj_orig(best) * 8;
     V3 outward; bool front; int mat;
     if (kind == RT_PRIM_PROGRAM) {
         const uint32_t code = best_code;
@@ -126,17 +152,38 @@ __device__ bool closest_hit(V3 o, V3 d, float tmin, float tmax, Hit& hit, Counte
 }
 
 // ---- Scene::occluded (scene.cpp:33-42) ---------------------------------------------------------------------
-template <bool C>
+template <bool C, bool K>
 __device__ bool occluded(V3 o, V3 d, float tmin, float tmax, Counters& cnt) {
     const int n_runs = c_hdr.n_runs;
     for (int r = 0; r < n_runs; ++r) {
         const int4 run = SV<C>::run(r);
         const int first = run.y, end = run.y + run.z;
-        if (run.x == RUN_SPHERE || run.x == RUN_POKEBALL) {
+        if (K && (run.x == RUN_SPHERE || run.x == RUN_POKEBALL) && run.w > 0) {     // clustered run (see closest_hit)
+            const int ctab = run.w - 1, ncl = (run.z + 15) >> 4;
+            cnt.tests += ncl;
+            for (int cb = 0; cb < ncl; cb += 32) {
+                uint32_t cmask = sphere_mask<C>(SV<C>::cluster_ptr(ctab + cb), min(32, ncl - cb), o, d);
+                while (cmask) {
+                    const int c = cb + __ffs(cmask) - 1; cmask &= cmask - 1;
+                    float hb;
+                    const float disc = sphere_disc(SV<C>::cluster(ctab + c), o, d, hb);
+                    const float sq = sqrtf(disc);
+                    if (-hb + sq < 0.f || -hb - sq > tmax) continue;
+                    const int m0 = first + 16 * c, n = min(16, end - m0);
+                    cnt.tests += n;
+                    uint32_t mask = sphere_mask<C>(SV<C>::obj_ptr(m0), n, o, d);
+                    while (mask) {
+                        const int i = m0 + __ffs(mask) - 1; mask &= mask - 1;
+                        float t;
+                        if (sphere_t(SV<C>::obj_geom(i), o, d, tmin, tmax, t)) return true;
+                    }
+                }
+            }
+        } else if (run.x == RUN_SPHERE || run.x == RUN_POKEBALL) {
             for (int c0 = first; c0 < end; c0 += 32) {                       // any-hit: early-out per chunk of 32
                 const int n = min(32, end - c0);
                 cnt.tests += n;
-                uint32_t mask = sphere_mask<C, false>(c0, n, o, d);
+                uint32_t mask = sphere_mask<C>(SV<C>::obj_ptr(c0), n, o, d);
                 while (mask) {
                     const int i = c0 + __ffs(mask) - 1; mask &= mask - 1;
                     float t;
@@ -165,7 +212,7 @@ __device__ __forceinline__ RGBf rgb(float r, float g, float b) { RGBf c; c.r = r
 __device__ __forceinline__ float screen1(float a, float b) { return 1.f - (1.f - a) * (1.f - b); }
 __device__ __forceinline__ RGBf screen(RGBf a, RGBf b) { return rgb(screen1(a.r, b.r), screen1(a.g, b.g), screen1(a.b, b.b)); }
 
-template <bool C>
+template <bool C, bool K>
 __device__ RGBf shade(const Hit& h, V3 p, V3 wo, Counters& cnt) {
     if (h.mat < 0) return rgb(1.f, 0.f, 1.f);                                // shading.cpp:33
     const float4 m0 = material(h.mat, 0), m1 = material(h.mat, 1), m2 = material(h.mat, 2);
@@ -187,7 +234,7 @@ __device__ RGBf shade(const Hit& h, V3 p, V3 wo, Counters& cnt) {
         float tmaxS = dist - eps;
         if (tmaxS <= eps) continue;
         ++cnt.shadow;
-        if (occluded<C>(so, normalized(wi), eps, tmaxS, cnt)) continue;      // Ray ctor re-normalises (core.h:278)
+        if (occluded<C, K>(so, normalized(wi), eps, tmaxS, cnt)) continue;      // Ray ctor re-normalises (core.h:278)
         float eff = fmaxf(0.5f, dist);
         float fall = 2.0f / (eff * eff);                                     // falloff * 2.0 (shading.cpp:108-112)
         RGBf I = rgb(li.x * fall, li.y * fall, li.z * fall);
@@ -215,12 +262,12 @@ struct Frame {
     float kt; V3 ro, rd;            // owed refraction (kt > 0 when owed)
 };
 
-template <bool C>
+template <bool C, bool K>
 __device__ RGBf trace(V3 o, V3 d, Hit* primary, bool* primary_hit, Counters& cnt) {
     const int limit = c_hdr.recursion;
     if (primary_hit) *primary_hit = false;
     if (limit <= 0) {                                                        // tracer.cpp:26 at depth 0
-        if (primary) { Hit h; *primary_hit = closest_hit<C>(o, d, 1e-4f, kInf, h, cnt); *primary = h; }
+        if (primary) { Hit h; *primary_hit = closest_hit<C, K>(o, d, 1e-4f, kInf, h, cnt); *primary = h; }
         return rgb(0.f, 0.f, 0.f);
     }
     Frame stack[RT_MAX_RECURSION];
@@ -229,7 +276,7 @@ __device__ RGBf trace(V3 o, V3 d, Hit* primary, bool* primary_hit, Counters& cnt
     for (;;) {
         // ---- evaluate the ray (o,d) at depth sp ----
         Hit h;
-        bool hit = closest_hit<C>(o, d, 1e-4f, kInf, h, cnt);                // tracer.cpp:29
+        bool hit = closest_hit<C, K>(o, d, 1e-4f, kInf, h, cnt);                // tracer.cpp:29
         if (sp == 0) { ++cnt.primary; if (primary) { *primary = h; *primary_hit = hit; } } else ++cnt.secondary;
         bool descend = false;
         if (!hit) {
@@ -237,7 +284,7 @@ __device__ RGBf trace(V3 o, V3 d, Hit* primary, bool* primary_hit, Counters& cnt
         } else {
             const V3 p = madd(o, d, h.t);
             const V3 wo = normalized(neg(d));
-            RGBf total = shade<C>(h, p, wo, cnt);                            // tracer.cpp:31
+            RGBf total = shade<C, K>(h, p, wo, cnt);                            // tracer.cpp:31
             result = total;
             if (h.mat >= 0 && sp < limit - 1) {
                 const float4 m1 = material(h.mat, 1), m2 = material(h.mat, 2);

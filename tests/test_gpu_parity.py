@@ -139,6 +139,33 @@ def test_global_memory_scene_path(gpu, oa):
     assert_parity(got, want["fb"], want["ids"], oa, "5600 spheres (global path)")
 
 
+def test_clustered_run_keeps_the_tie_rule(gpu, oa):
+    """A long run of spheres is scanned through spatial clusters; exact ties (duplicated spheres) must still go to the
+    later JSON object, as in the reference's linear scan with an inclusive window (scene.cpp:15-21, geometry.cpp:26-28)."""
+    rng = np.random.default_rng(11)
+    def sph(x, y, z, r, c):
+        return {"sphere": {"position": [float(x), float(y), float(z)], "radius": float(r),
+                           "color": {"diffuse": [float(c), 0.5, 1.0 - float(c)], "specular": [0.2] * 3, "shininess": 8}}}
+    pts = np.c_[rng.uniform(-6, 6, 400), rng.uniform(-4, 4, 400), rng.uniform(-14, -4, 400), rng.uniform(0.15, 0.5, 400)]
+    objs = [sph(*p, c) for p, c in zip(pts, rng.uniform(0, 1, 400))]
+    objs += [sph(*pts[k], 0.0) for k in range(0, 400, 7)]                      # exact duplicates, later in JSON order
+    scene = {"screen": {"dpi": 24, "dimensions": [4, 3], "position": [-2, -1.5, 0], "observer": [0, 0, 4]},
+             "medium": {"ambient": [0.3, 0.3, 0.3], "recursion": 3}, "background": [0.1, 0.2, 0.3],
+             "sources": [{"position": [3, 5, 6], "intensity": [30, 30, 30]}, {"position": [-4, 2, 3], "intensity": [20, 20, 20]}],
+             "objects": objs}
+    text = json.dumps(scene)
+    sc = gpu.load_scene_from_json_text(text)
+    _, runs, clusters = sc.device_layout()
+    assert len(clusters) > 0, "the run must be clustered for this test to mean anything"
+    got, _ = render_gpu(gpu, sc, "standard")
+    want = oa.Oracle(text).render("standard", want_ids=True)
+    assert (want["ids"] // 8 >= 400).any(), "duplicates must be visible in the reference"
+    assert_parity(got, want["fb"], want["ids"], oa, "457 spheres with exact duplicates (clustered)")
+    got, _ = render_gpu(gpu, sc, "paper")
+    want = oa.Oracle(text).render("paper", want_ids=True)
+    assert_parity(got, want["fb"], want["ids"], oa, "457 spheres with exact duplicates (clustered, paper)")
+
+
 @pytest.mark.parametrize("name,bands", [("snorlax_4k", [(0, 2), (1079, 1082), (1500, 1502), (2158, 2160)]),
                                         ("snorlax_4k_reflect", [(900, 903)]), ("penguin_4k", [(1000, 1003)])])
 def test_full_resolution_bands_match_oracle(gpu, oa, name, bands):
