@@ -195,7 +195,8 @@ int rt_debug_mt_block_host(uint32_t seed, uint64_t block, uint32_t* out624);
 /* HOST-ONLY view of the device layout rt_scene_upload builds (no GPU needed).  Long runs of plain spheres /
  * pokeballs are reordered spatially and get one bounding sphere per 16 primitives (the reference scans linearly,
  * scene.cpp:10-42; results are identical).  order[i] = JSON index of device object i; runs4 = (kind,
- * first, count, 1 + first cluster or 0) per run; clusters4 = (cx, cy, cz, R) per cluster.  Outputs may be NULL. */
+ * first, count, 1 + first bound or 0) per run; clusters4 = (cx, cy, cz, R): one bound per 16 primitives of a clustered
+ * run, one per object of a long run of generic objects (at most n_objects + n_objects/16 + 1 in all).  Outputs may be NULL. */
 int rt_debug_device_layout(const rt_scene_desc* desc, int* order, int* n_runs, int* runs4, int* n_clusters, float* clusters4);
 
 /* Measured FP32 FFMA peak of the current device in TFLOP/s (dependent-free FFMA micro-benchmark). */

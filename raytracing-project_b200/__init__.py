@@ -179,7 +179,7 @@ class Scene:
         """(order, runs[n,4], clusters[m,4]) of the device layout (host-only; see rt_debug_device_layout)."""
         n = int(self.desc.n_objects)
         order = np.zeros(max(n, 1), np.int32); runs = np.zeros((max(n, 1), 4), np.int32)
-        clusters = np.zeros((n // 16 + 2, 4), np.float32); nr, nc = C.c_int(), C.c_int()
+        clusters = np.zeros((n + n // 16 + 2, 4), np.float32); nr, nc = C.c_int(), C.c_int()
         _check(lib().rt_debug_device_layout(C.byref(self.desc), order.ctypes.data_as(C.c_void_p), C.byref(nr),
                                             runs.ctypes.data_as(C.c_void_p), C.byref(nc), clusters.ctypes.data_as(C.c_void_p)))
         return order[:n], runs[: nr.value], clusters[: nc.value]

@@ -6,6 +6,7 @@
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <limits>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -29,6 +30,10 @@ struct Context {
     uint32_t* mt_resume{nullptr};
     unsigned long long* counters{nullptr}; unsigned* tile_counter{nullptr};
     const void* const_owner{nullptr};     // which scene currently occupies constant memory
+    // frame buffers of the host-output path (rt_render): owned by the context and grown on demand, so that a
+    // fresh scene (the CLI, the bench's end-to-end leg) does not pay cudaMalloc/cudaFree of ~100 MB per frame
+    uchar4* d_rgba8{nullptr}; float4* d_rgbf{nullptr}; int* d_ids{nullptr}; rtd::GBuf* d_gbuf{nullptr}; unsigned char* d_pack{nullptr};
+    size_t rgba8_cap{0}, rgbf_cap{0}, ids_cap{0}, gbuf_cap{0}, pack_cap{0};     // bytes
     std::mutex mu;
 };
 Context g_ctx;
@@ -58,9 +63,6 @@ struct rt_scene {
     int4 *d_obj_meta{nullptr}, *d_leaf_meta{nullptr}, *d_runs{nullptr};
     uint32_t* d_ops{nullptr};
     int width{0}, height{0};
-    // device frame buffers (lazily sized)
-    uchar4* d_rgba8{nullptr}; float4* d_rgbf{nullptr}; int* d_ids{nullptr}; rtd::GBuf* d_gbuf{nullptr};
-    unsigned char* d_pack{nullptr}; size_t pack_bytes{0}; size_t ids_elems{0};
 };
 
 namespace {
@@ -76,6 +78,7 @@ int4 meta_of(const rt_prim& p) { return make_int4((p.kind & 0xff) | (p.flags << 
 // the scan order and exact ties are resolved by JSON index on the device (obj_orig).
 constexpr int kClusterSize = 16;      // the device code shifts by 4
 constexpr int kClusterMinRun = 48;
+constexpr int kGenericBoundMinRun = 8;  // runs of generic objects this long get a per-object world bound
 
 void split_run(std::vector<int>& idx, int lo, int hi, const rt_prim* objs) {
     if (hi - lo <= kClusterSize) return;
@@ -178,10 +181,27 @@ void build_host_arrays(const rt_scene_desc& d, rt_scene& s) {
     for (int i = 0; i < d.n_objects;) {
         const rt_prim& p = d.objects[i];
         const bool plain = p.flags == 0 && p.kind != RT_PRIM_PROGRAM;
-        if (!plain) {
-            if (!s.runs.empty() && s.runs.back().x == rtd::RUN_GENERIC && s.runs.back().y + s.runs.back().z == i) s.runs.back().z++;
-            else s.runs.push_back(make_int4(rtd::RUN_GENERIC, i, 1, 0));
-            ++i; continue;
+        if (!plain) {                      // maximal run of generic objects (CSG programs, transform-wrapped / affine primitives)
+            int j = i; while (j < d.n_objects && !(d.objects[j].flags == 0 && d.objects[j].kind != RT_PRIM_PROGRAM)) ++j;
+            int ctab = 0;
+            if (j - i >= kGenericBoundMinRun) {
+                // one conservative WORLD bounding sphere per object (R = inf: unknown), scanned with the candidate mask
+                // before the object itself is looked at
+                ctab = (int)s.clusters.size() + 1;
+                for (int k = i; k < j; ++k) {
+                    const rt_prim& q = d.objects[k];
+                    float4 b = make_float4(0.f, 0.f, 0.f, std::numeric_limits<float>::infinity());
+                    const bool finite = std::isfinite(q.geom[0]) && std::isfinite(q.geom[1]) && std::isfinite(q.geom[2]) && std::isfinite(q.geom[3]);
+                    if (q.kind == RT_PRIM_PROGRAM) { if (q.geom[3] >= 0.f && finite) b = make_float4(q.geom[0], q.geom[1], q.geom[2], q.geom[3]); }
+                    else if (q.kind != RT_PRIM_HALFSPACE && !(q.flags & RT_FLAG_AFFINE) && finite) {
+                        int one = k;                // baked similarity transforms: geom is the world-space sphere
+                        b = bound_of(d.objects, &one, 1);
+                    }
+                    s.clusters.push_back(b);
+                }
+            }
+            s.runs.push_back(make_int4(rtd::RUN_GENERIC, i, j - i, ctab));
+            i = j; continue;
         }
         int j = i; while (j < d.n_objects && d.objects[j].flags == 0 && d.objects[j].kind == p.kind) ++j;
         const int kind = p.kind == RT_PRIM_SPHERE ? rtd::RUN_SPHERE : p.kind == RT_PRIM_HALFSPACE ? rtd::RUN_HALFSPACE : rtd::RUN_POKEBALL;
@@ -233,6 +253,9 @@ void rt_shutdown(void) {
     if (!g_ctx.ready) return;
     cudaSetDevice(g_ctx.device);
     cudaFree(g_ctx.mt_table); cudaFree(g_ctx.mt_resume); cudaFree(g_ctx.counters); cudaFree(g_ctx.tile_counter);
+    cudaFree(g_ctx.d_rgba8); cudaFree(g_ctx.d_rgbf); cudaFree(g_ctx.d_ids); cudaFree(g_ctx.d_gbuf); cudaFree(g_ctx.d_pack);
+    g_ctx.d_rgba8 = nullptr; g_ctx.d_rgbf = nullptr; g_ctx.d_ids = nullptr; g_ctx.d_gbuf = nullptr; g_ctx.d_pack = nullptr;
+    g_ctx.rgba8_cap = g_ctx.rgbf_cap = g_ctx.ids_cap = g_ctx.gbuf_cap = g_ctx.pack_cap = 0;
     cudaEventDestroy(g_ctx.ev0); cudaEventDestroy(g_ctx.ev1); cudaStreamDestroy(g_ctx.stream);
     g_ctx.ready = false; g_ctx.device = -1; g_ctx.mt_table = nullptr; g_ctx.mt_tiles = 0; g_ctx.mt_capacity = 0;
     g_ctx.mt_resume = nullptr; g_ctx.counters = nullptr; g_ctx.tile_counter = nullptr; g_ctx.const_owner = nullptr;
@@ -284,14 +307,13 @@ void rt_scene_free(rt_scene* s) {
     cudaFree(s->d_obj_geom); cudaFree(s->d_obj_meta); cudaFree(s->d_leaf_geom); cudaFree(s->d_leaf_meta);
     cudaFree(s->d_pokeballs); cudaFree(s->d_affines); cudaFree(s->d_ops); cudaFree(s->d_materials);
     cudaFree(s->d_lights); cudaFree(s->d_fallbacks); cudaFree(s->d_runs); cudaFree(s->d_clusters); cudaFree(s->d_obj_orig);
-    cudaFree(s->d_rgba8); cudaFree(s->d_rgbf); cudaFree(s->d_ids); cudaFree(s->d_gbuf); cudaFree(s->d_pack);
     delete s;
 }
 
 // Host-only view of the device layout rt_scene_upload would build (no GPU needed): the permutation of the top-level
 // objects, the runs (kind, first, count, 1 + first cluster | 0) and the cluster bounds.  Any output may be NULL.
 int rt_debug_device_layout(const rt_scene_desc* d, int* order /*n_objects*/, int* n_runs, int* runs4 /*<= n_objects x 4*/,
-                           int* n_clusters, float* clusters4 /*<= n_objects/16+1 x 4*/) {
+                           int* n_clusters, float* clusters4 /*<= n_objects + n_objects/16 + 1, x 4*/) {
     if (!d) return fail(RT_ERR_ARG, "rt_debug_device_layout: null scene");
     rt_scene s;
     build_host_arrays(*d, s);
@@ -345,16 +367,20 @@ int ensure_mt_table(long long tiles) {
 
 namespace {
 
+template <class T> int grow(T** p, size_t* cap, size_t bytes) {
+    if (*cap >= bytes) return RT_OK;
+    cudaFree(*p); *p = nullptr; *cap = 0;
+    CU(cudaMalloc((void**)p, bytes));
+    *cap = bytes;
+    return RT_OK;
+}
+
 int ensure_frame_buffers(rt_scene* s, bool want_f, bool want_ids, int mode) {
     const size_t npx = (size_t)s->width * s->height;
-    if (!s->d_rgba8) CU(cudaMalloc((void**)&s->d_rgba8, npx * sizeof(uchar4)));
-    if (want_f && !s->d_rgbf) CU(cudaMalloc((void**)&s->d_rgbf, npx * sizeof(float4)));
-    const size_t need_ids = npx * (mode == RT_MODE_PAPER ? 1 : 8);
-    if (want_ids && s->ids_elems < need_ids) {
-        cudaFree(s->d_ids); s->d_ids = nullptr;
-        CU(cudaMalloc((void**)&s->d_ids, need_ids * sizeof(int))); s->ids_elems = need_ids;
-    }
-    if (mode == RT_MODE_PAPER && !s->d_gbuf) CU(cudaMalloc((void**)&s->d_gbuf, npx * sizeof(rtd::GBuf)));
+    int rc = grow(&g_ctx.d_rgba8, &g_ctx.rgba8_cap, npx * sizeof(uchar4)); if (rc) return rc;
+    if (want_f && (rc = grow(&g_ctx.d_rgbf, &g_ctx.rgbf_cap, npx * sizeof(float4)))) return rc;
+    if (want_ids && (rc = grow(&g_ctx.d_ids, &g_ctx.ids_cap, npx * (mode == RT_MODE_PAPER ? 1 : 8) * sizeof(int)))) return rc;
+    if (mode == RT_MODE_PAPER && (rc = grow(&g_ctx.d_gbuf, &g_ctx.gbuf_cap, npx * sizeof(rtd::GBuf)))) return rc;
     return RT_OK;
 }
 
@@ -364,13 +390,13 @@ int launch_frame(rt_scene* s, int mode, int rank, int world, uchar4* rgba8, floa
     int rc = bind_scene(s, st); if (rc) return rc;
     CU(cudaMemsetAsync(g_ctx.counters, 0, 4 * sizeof(unsigned long long), st));
     if (mode == RT_MODE_PAPER) {
-        if (!s->d_gbuf) CU(cudaMalloc((void**)&s->d_gbuf, (size_t)npx * sizeof(rtd::GBuf)));
+        { int rc2 = grow(&g_ctx.d_gbuf, &g_ctx.gbuf_cap, (size_t)npx * sizeof(rtd::GBuf)); if (rc2) return rc2; }
         const unsigned blocks = (unsigned)((npx + 255) / 256);
         // kernel variant: <scene staged in shared memory, scene has clustered runs>
         auto paper = s->fits_const ? (s->clusters.empty() ? rtd::paper_gbuffer_kernel<true, false> : rtd::paper_gbuffer_kernel<true, true>)
                                    : (s->clusters.empty() ? rtd::paper_gbuffer_kernel<false, false> : rtd::paper_gbuffer_kernel<false, true>);
-        paper<<<blocks, 256, s->fits_const ? s->smem_bytes : 0, st>>>(s->d_gbuf, ids, g_ctx.counters, rank, world);
-        rtd::paper_post_kernel<<<blocks, 256, 0, st>>>(s->d_gbuf, rgba8, rgbf, s->width, s->height, rank, world);
+        paper<<<blocks, 256, s->fits_const ? s->smem_bytes : 0, st>>>(g_ctx.d_gbuf, ids, g_ctx.counters, rank, world);
+        rtd::paper_post_kernel<<<blocks, 256, 0, st>>>(g_ctx.d_gbuf, rgba8, rgbf, s->width, s->height, rank, world);
         CU(cudaGetLastError());
         if (n_tiles_out) *n_tiles_out = (s->height + rtd::kPaperRows - 1) / rtd::kPaperRows;
         return RT_OK;
@@ -459,37 +485,30 @@ int rt_render(rt_scene* s, int mode, int rank, int world, uint8_t* rgb8, float* 
     if (mode == RT_MODE_STANDARD) { rc = ensure_mt_table((npx + mt::kPixelsPerTile - 1) / mt::kPixelsPerTile); if (rc) return rc; }
     rc = bind_scene(s, st); if (rc) return rc;
     if (world > 1) {   // pixels of other ranks: defined (zero / -1) so that slices can be summed or compared
-        CU(cudaMemsetAsync(s->d_rgba8, 0, (size_t)npx * sizeof(uchar4), st));
-        if (rgbf) CU(cudaMemsetAsync(s->d_rgbf, 0, (size_t)npx * sizeof(float4), st));
-        if (ids) CU(cudaMemsetAsync(s->d_ids, 0xff, s->ids_elems * sizeof(int), st));
+        CU(cudaMemsetAsync(g_ctx.d_rgba8, 0, (size_t)npx * sizeof(uchar4), st));
+        if (rgbf) CU(cudaMemsetAsync(g_ctx.d_rgbf, 0, (size_t)npx * sizeof(float4), st));
+        if (ids) CU(cudaMemsetAsync(g_ctx.d_ids, 0xff, (size_t)npx * (mode == RT_MODE_PAPER ? 1 : 8) * sizeof(int), st));
     }
     int n_tiles = 0;
     CU(cudaEventRecord(g_ctx.ev0, st));
-    rc = launch_frame(s, mode, rank, world, s->d_rgba8, rgbf ? s->d_rgbf : nullptr, ids ? s->d_ids : nullptr, st, &n_tiles);
+    rc = launch_frame(s, mode, rank, world, g_ctx.d_rgba8, rgbf ? g_ctx.d_rgbf : nullptr, ids ? g_ctx.d_ids : nullptr, st, &n_tiles);
     if (rc) return rc;
     CU(cudaEventRecord(g_ctx.ev1, st));
     const unsigned blocks = (unsigned)((npx + 255) / 256);
     if (rgb8) {
         const size_t need = (size_t)npx * 3;
-        if (s->pack_bytes < std::max(need, (size_t)npx * 12)) {
-            cudaFree(s->d_pack); s->d_pack = nullptr;
-            s->pack_bytes = std::max(need, (size_t)npx * 12);
-            CU(cudaMalloc((void**)&s->d_pack, s->pack_bytes));
-        }
-        rtd::pack_rgb_kernel<<<blocks, 256, 0, st>>>(s->d_rgba8, s->d_pack, npx);
-        CU(cudaMemcpyAsync(rgb8, s->d_pack, need, cudaMemcpyDeviceToHost, st));
+        rc = grow(&g_ctx.d_pack, &g_ctx.pack_cap, std::max(need, (size_t)npx * 12)); if (rc) return rc;
+        rtd::pack_rgb_kernel<<<blocks, 256, 0, st>>>(g_ctx.d_rgba8, g_ctx.d_pack, npx);
+        CU(cudaMemcpyAsync(rgb8, g_ctx.d_pack, need, cudaMemcpyDeviceToHost, st));
         CU(cudaStreamSynchronize(st));
     }
     if (rgbf) {
-        if (s->pack_bytes < (size_t)npx * 12) {
-            cudaFree(s->d_pack); s->d_pack = nullptr; s->pack_bytes = (size_t)npx * 12;
-            CU(cudaMalloc((void**)&s->d_pack, s->pack_bytes));
-        }
-        rtd::unpack_rgbf_kernel<<<blocks, 256, 0, st>>>(s->d_rgbf, (float*)s->d_pack, npx);
-        CU(cudaMemcpyAsync(rgbf, s->d_pack, (size_t)npx * 12, cudaMemcpyDeviceToHost, st));
+        rc = grow(&g_ctx.d_pack, &g_ctx.pack_cap, (size_t)npx * 12); if (rc) return rc;
+        rtd::unpack_rgbf_kernel<<<blocks, 256, 0, st>>>(g_ctx.d_rgbf, (float*)g_ctx.d_pack, npx);
+        CU(cudaMemcpyAsync(rgbf, g_ctx.d_pack, (size_t)npx * 12, cudaMemcpyDeviceToHost, st));
         CU(cudaStreamSynchronize(st));
     }
-    if (ids) CU(cudaMemcpyAsync(ids, s->d_ids, (size_t)npx * (mode == RT_MODE_PAPER ? 1 : 8) * sizeof(int), cudaMemcpyDeviceToHost, st));
+    if (ids) CU(cudaMemcpyAsync(ids, g_ctx.d_ids, (size_t)npx * (mode == RT_MODE_PAPER ? 1 : 8) * sizeof(int), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     CU(cudaGetLastError());
     float ms = 0.f; CU(cudaEventElapsedTime(&ms, g_ctx.ev0, g_ctx.ev1));

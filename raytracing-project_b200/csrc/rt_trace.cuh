@@ -106,6 +106,17 @@ __device__ bool closest_hit(V3 o, V3 d, float tmin, float tmax, Hit& hit, Counte
                 float t;
                 if (plane_t(SV<C>::obj_geom(i), o, d, tmin, best_t, t)) { best = i; best_t = t; }
             }
+        } else if (K && run.w > 0) {                   // generic run with per-object world bounds: candidates only
+            const int ctab = run.w - 1;
+            cnt.tests += run.z;
+            for (int c0 = first; c0 < end; c0 += 32) {
+                uint32_t mask = sphere_mask<C>(SV<C>::cluster_ptr(ctab + c0 - first), min(32, end - c0), o, d);
+                while (mask) {
+                    const int i = c0 + __ffs(mask) - 1; mask &= mask - 1;
+                    float t, tent; uint32_t code;
+                    if (generic_hit<C>(i, o, d, tmin, best_t, t, code, tent, cnt.tests)) { best = i; best_t = t; best_code = code; best_tent = tent; }
+                }
+            }
         } else {
             for (int i = first; i < end; ++i) {
                 float t, tent; uint32_t code;
@@ -194,6 +205,17 @@ __device__ bool occluded(V3 o, V3 d, float tmin, float tmax, Counters& cnt) {
             for (int i = first; i < end; ++i) {
                 float t; ++cnt.tests;
                 if (plane_t(SV<C>::obj_geom(i), o, d, tmin, tmax, t)) return true;
+            }
+        } else if (K && run.w > 0) {                   // generic run with per-object world bounds: candidates only
+            const int ctab = run.w - 1;
+            cnt.tests += run.z;
+            for (int c0 = first; c0 < end; c0 += 32) {
+                uint32_t mask = sphere_mask<C>(SV<C>::cluster_ptr(ctab + c0 - first), min(32, end - c0), o, d);
+                while (mask) {
+                    const int i = c0 + __ffs(mask) - 1; mask &= mask - 1;
+                    float t, tent; uint32_t code;
+                    if (generic_hit<C>(i, o, d, tmin, tmax, t, code, tent, cnt.tests)) return true;
+                }
             }
         } else {
             for (int i = first; i < end; ++i) {

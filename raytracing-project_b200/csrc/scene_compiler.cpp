@@ -279,10 +279,32 @@ public:
         ops.swap(out);
     }
 
-    // Conservative bounding sphere of a program's leaves (baked to world space), inflated well beyond the FP32
-    // rounding of the device's discriminant, so that "misses the bound" implies "misses every leaf" on the device.
-    // Only when every leaf is a sphere/pokeball in world space; a half-space is unbounded, and a leaf under a
-    // non-uniform scaling is an ellipsoid (left unbounded here).
+    // World-space bounding sphere of a sphere-like leaf.  Baked leaves are world spheres already; a leaf under a
+    // non-uniform scaling is the ellipsoid { x : |A x + b - c| <= r }, bounded by centre A^-1 (c - b) and radius
+    // r * ||A^-1||_F (>= r * sigma_max(A^-1)).
+    bool leaf_world_sphere(const rt_prim& l, double c[3], double& R) const {
+        if (l.kind == RT_PRIM_HALFSPACE) return false;
+        if (!(l.flags & RT_FLAG_AFFINE)) {
+            c[0] = l.geom[0]; c[1] = l.geom[1]; c[2] = l.geom[2]; R = std::abs((double)l.geom[3]);
+            return true;
+        }
+        const rt_affine& a = affines[(size_t)l.xf];
+        double A[3][3], Ai[3][3];
+        for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) A[i][j] = a.m[i][j];
+        if (!invert3(A, Ai)) return false;
+        const double v[3] = {l.geom[0] - a.m[0][3], l.geom[1] - a.m[1][3], l.geom[2] - a.m[2][3]};
+        double f2 = 0;
+        for (int i = 0; i < 3; ++i) {
+            c[i] = Ai[i][0] * v[0] + Ai[i][1] * v[1] + Ai[i][2] * v[2];
+            for (int j = 0; j < 3; ++j) f2 += Ai[i][j] * Ai[i][j];
+        }
+        R = std::abs((double)l.geom[3]) * std::sqrt(f2);
+        return std::isfinite(R);
+    }
+
+    // Conservative bounding sphere of a program's leaves, inflated well beyond the FP32 rounding of the device's
+    // discriminant, so that "misses the bound" implies "misses every leaf" on the device.  None when a leaf is a
+    // half-space (unbounded).
     void bound_program(rt_prim& p, size_t leaf0) const {
         p.geom[0] = p.geom[1] = p.geom[2] = 0.f; p.geom[3] = -1.f;
         double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
@@ -290,25 +312,25 @@ public:
         for (size_t i = leaf0; i < leaves.size(); ++i) {
             const rt_prim& l = leaves[i];
             if (l.flags & RT_FLAG_NEVER) continue;
-            if (l.kind == RT_PRIM_HALFSPACE || (l.flags & RT_FLAG_AFFINE)) return;
-            for (int k = 0; k < 3; ++k) {
-                lo[k] = std::min(lo[k], (double)l.geom[k] - std::abs((double)l.geom[3]));
-                hi[k] = std::max(hi[k], (double)l.geom[k] + std::abs((double)l.geom[3]));
-            }
+            double c[3], R;
+            if (!leaf_world_sphere(l, c, R)) return;
+            for (int k = 0; k < 3; ++k) { lo[k] = std::min(lo[k], c[k] - R); hi[k] = std::max(hi[k], c[k] + R); }
             ++n;
         }
         if (n == 0) return;
-        const double c[3] = {0.5 * (lo[0] + hi[0]), 0.5 * (lo[1] + hi[1]), 0.5 * (lo[2] + hi[2])};
-        double R = 0;
+        const double ctr[3] = {0.5 * (lo[0] + hi[0]), 0.5 * (lo[1] + hi[1]), 0.5 * (lo[2] + hi[2])};
+        double Rmax = 0;
         for (size_t i = leaf0; i < leaves.size(); ++i) {
             const rt_prim& l = leaves[i];
             if (l.flags & RT_FLAG_NEVER) continue;
-            const double dx = l.geom[0] - c[0], dy = l.geom[1] - c[1], dz = l.geom[2] - c[2];
-            R = std::max(R, std::sqrt(dx * dx + dy * dy + dz * dz) + std::abs((double)l.geom[3]));
+            double c[3] = {0, 0, 0}, R = 0;
+            leaf_world_sphere(l, c, R);
+            const double dx = c[0] - ctr[0], dy = c[1] - ctr[1], dz = c[2] - ctr[2];
+            Rmax = std::max(Rmax, std::sqrt(dx * dx + dy * dy + dz * dz) + R);
         }
-        if (!std::isfinite(R)) return;
-        p.geom[0] = (float)c[0]; p.geom[1] = (float)c[1]; p.geom[2] = (float)c[2];
-        p.geom[3] = (float)(R * 1.002 + 1e-3);
+        if (!std::isfinite(Rmax)) return;
+        p.geom[0] = (float)ctr[0]; p.geom[1] = (float)ctr[1]; p.geom[2] = (float)ctr[2];
+        p.geom[3] = (float)(Rmax * 1.002 + 1e-3);
     }
 
     void add_object(const Node& top) {

@@ -33,9 +33,15 @@ def test_cluster_bounds_contain_their_members(rt):
     sc = rt.load_scene_from_json(scene_path("synthetic_a_small"))
     order, runs, clusters = sc.device_layout()
     objs = sc.objects()
-    clustered = [r for r in runs.tolist() if r[3] > 0]
+    clustered = [r for r in runs.tolist() if r[3] > 0 and r[0] != 3]
     assert len(clustered) == 2 and [r[2] for r in clustered] == [1000, 64]      # 1 000 spheres and 64 pokeballs
-    assert len(clusters) == 63 + 4
+    generic = [r for r in runs.tolist() if r[0] == 3]
+    assert len(generic) == 1 and generic[0][2] == 32 and generic[0][3] > 0        # 32 CSG programs: one world bound each
+    assert len(clusters) == 63 + 4 + 32
+    g0 = generic[0]
+    for k in range(32):
+        prog = objs[g0[1] + k]
+        assert prog.kind == 3 and list(clusters[g0[3] - 1 + k]) == pytest.approx(list(prog.geom))
     for kind, first, count, ctab in clustered:
         for c in range((count + 15) // 16):
             cx, cy, cz, R = clusters[ctab - 1 + c]
