@@ -36,6 +36,23 @@ REF_DRIVER = os.path.join(ROOT, "oracle", "_ref", "ref_driver")
 FLOP_PRIM_TEST, FLOP_SHADOW, FLOP_QUERY, FLOP_PIXEL = 17, 80, 30, 12
 
 
+def traffic_of(workload: str, paper: bool):
+    """DRAM bytes per launch of the dominant kernel from this round's `ncu --set full` capture (profiles/traffic.json)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f).get(workload + (":paper" if paper else ""))
+    except Exception:
+        return None
+
+
+def hbm_peak_gbs():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return json.load(f)["hbm_gbs"]
+    except Exception:
+        return 6650.0      # B200_PROFILING.md fallback
+
+
 def flops_of(stats: dict, pixels: int) -> float:
     return (FLOP_PRIM_TEST * stats["prim_tests"] + FLOP_SHADOW * stats["shadow_rays"]
             + FLOP_QUERY * (stats["primary_rays"] + stats["secondary_rays"]) + FLOP_PIXEL * pixels)
@@ -131,9 +148,11 @@ def run_reference(args) -> None:
     sample = f"{last['rows']} rows (y % {last['stride']} in {threads} offsets) of {W}x{H}, one single-threaded process per core"
     print(json.dumps({
         "impl": "reference", "metric": "Mrays/s", "value": v, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": float(np.mean(step_ms)), "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": float(np.mean(step_ms)), "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": os.path.basename(args.scene), "width": W, "height": H, "spp": 8, "step": "bounded row sample of one frame"},
+        "config": {"workload": os.path.basename(args.scene), "width": W, "height": H, "spp": 8, "mode": "standard",
+                   "step": "bounded row sample of one frame (the reference cannot render a sub-frame faster than its RNG stream: rows "
+                           "are sampled with rng.discard, oracle/ref_driver.cpp), one single-threaded process per host core"},
         "ms_per_frame_extrapolated": frame_rays_est / (v * 1e6) * 1e3,
         "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": threads, "kind": last["kind"], "sample": sample},
         "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -298,9 +317,14 @@ def run_ours(args) -> None:
             "e2e": {"value": rays_per_frame / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_frame": e2e_ms,
                     "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(W * H * (3 if world == 1 else 4))},
             "gpu_launches": args.steps * (2 if args.paper else 1) * world,
+            # north_star: this path is FP32 CUDA-core work, reported against the FP32 roofline.  MEASURED_PEAKS.json holds
+            # only HBM and bf16-tensor peaks, so the denominator is measured live on this GPU (FFMA micro-benchmark).
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak_tflops, "unit": "TFLOP/s", "frac": achieved / peak_tflops,
-                         "traffic": None, "peak_source": "measured live (dependent-free FFMA micro-benchmark, rt_measure_fp32_peak)",
-                         "flops_per_frame": flops},
+                         "traffic": traffic_of(os.path.basename(args.scene), args.paper),
+                         "peak_source": "measured live (dependent-free FFMA micro-benchmark, rt_measure_fp32_peak)",
+                         "flops_per_frame": flops,
+                         "framebuffer": {"bytes_per_frame": int(W * H * 4), "achieved_gbs": W * H * 4 / (kernel_ms * 1e-3) / 1e9 / world,
+                                         "hbm_peak_gbs": hbm_peak_gbs(), "note": "RGBA8 stores only; the frame is compute-bound"}},
             "clocks": clocks,
         }
         if world == 1 and not args.no_cpu:

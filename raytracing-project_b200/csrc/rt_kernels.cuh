@@ -100,10 +100,15 @@ __device__ __forceinline__ void flush_counters(const Counters& c, unsigned long 
     }
 }
 
+// 4 CTAs x 256 threads per SM = 64 registers per thread: occupancy (32 warps/SM) is worth more here than registers;
+// measured against 2 (128 regs) and 3 (80 regs) on four scenes, see profiles/.
+#ifndef RT_MIN_BLOCKS
+#define RT_MIN_BLOCKS 4
+#endif
 constexpr int kRenderThreads = 256;
 
 template <bool C, bool K>
-__global__ void __launch_bounds__(kRenderThreads) render_standard_kernel(RenderParams prm) {
+__global__ void __launch_bounds__(kRenderThreads, RT_MIN_BLOCKS) render_standard_kernel(RenderParams prm) {
     __shared__ uint32_t st[2][mt::kN];
     __shared__ __align__(16) uint32_t outw[mt::kOutputsPerTile];
     __shared__ int s_tile;

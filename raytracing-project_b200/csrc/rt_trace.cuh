@@ -267,7 +267,8 @@ __device__ RGBf shade(const Hit& h, V3 p, V3 wo, Counters& cnt) {
             float two = 2.f * dot(n, wi);
             V3 rr = normalized(mk(fmaf(two, n.x, -wi.x), fmaf(two, n.y, -wi.y), fmaf(two, n.z, -wi.z)));
             float rdotv = fmaxf(0.f, dot(rr, wo));
-            float spec = powf(rdotv, shininess) * ks;
+            // exp2(s * log2(x)) on the MUFU pipe (relative error ~ s * 2^-21, far below 1/255); x == 0 keeps powf's edge cases
+            float spec = (rdotv > 0.f ? __powf(rdotv, shininess) : powf(rdotv, shininess)) * ks;
             Es = rgb(I.r * spec, I.g * spec, I.b * spec);
         }
         E = screen(E, screen(Ed, Es));
