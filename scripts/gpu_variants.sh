@@ -5,8 +5,9 @@ OUT=gpurun_out/$TAG; mkdir -p $OUT
 cp raytracing-project_b200/librt_b200.so /tmp/default.so
 for v in "$@"; do
   cp raytracing-project_b200/variants/$v.so raytracing-project_b200/librt_b200.so
-  for sc in $SCENES; do
-    python scripts/profile_run.py scenes/$sc.json standard 4 2>&1 | tail -1 | python -c "import sys,ast; d=ast.literal_eval(sys.stdin.read().strip()); print('$v','$sc','kernel_ms',round(d['kernel_ms'],3))" | tee -a $OUT/variants.txt
+  for a in $SCENES; do
+    sc=${a%%:*}; mode=standard; [[ "$a" == *:* ]] && mode=${a##*:}
+    python scripts/profile_run.py scenes/$sc.json $mode 4 2>&1 | tail -1 | python -c "import sys,ast; d=ast.literal_eval(sys.stdin.read().strip()); print('$v','$a','kernel_ms',round(d['kernel_ms'],3))" | tee -a $OUT/variants.txt
   done
 done
 cp /tmp/default.so raytracing-project_b200/librt_b200.so
