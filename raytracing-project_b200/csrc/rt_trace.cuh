@@ -365,4 +365,80 @@ __device__ RGBf trace(V3 o, V3 d, Hit* primary, bool* primary_hit, Counters& cnt
     }
 }
 
+// ---- one ray of a sample whose tree state lives in global memory (wavefront kernel) -----------------------------------
+// Same logic as the loop body of trace(); the pending parents are 3 float4 per depth in global memory
+// (total.rgb k_pending | kt ro.xyz | rd.xyz -), so ANY thread can take ANY unfinished sample from the CTA's queue.
+// Returns true when the tree is finished (`result` = Tracer::trace's colour), false when (o, d, sp) is the next ray.
+template <bool C, bool K>
+__device__ __forceinline__ bool advance_ray(V3& o, V3& d, int& sp, float4* __restrict__ frames, RGBf& result,
+                                            Hit& primary, bool& primary_hit, Counters& cnt) {
+    const int limit = c_hdr.recursion;
+    Hit h;
+    const bool hit = closest_hit<C, K>(o, d, 1e-4f, kInf, h, cnt);           // tracer.cpp:29
+    if (sp == 0) { ++cnt.primary; primary = h; primary_hit = hit; } else ++cnt.secondary;
+    if (!hit) {
+        result = rgb(c_hdr.bg[0], c_hdr.bg[1], c_hdr.bg[2]);                 // tracer.cpp:72
+    } else {
+        const V3 p = madd(o, d, h.t);
+        const V3 wo = normalized(neg(d));
+        const RGBf total = shade<C, K>(h, p, wo, cnt);                       // tracer.cpp:31
+        result = total;
+        if (h.mat >= 0 && sp < limit - 1) {
+            const float4 m1 = material(h.mat, 1), m2 = material(h.mat, 2);
+            const float kr = m1.w, kt = m2.x, ior = m2.z;
+            const V3 I = normalized(d);
+            bool want_r = kr > 0.f, want_t = false;
+            V3 to = mk(0.f, 0.f, 0.f), td = mk(0.f, 0.f, 0.f);
+            if (kt > 0.f) {                                                  // tracer.cpp:51-68
+                float eta = h.front ? (c_hdr.medium_index / ior) : (ior / c_hdr.medium_index);
+                float cos_i = -dot(I, h.n);
+                float sin_t2 = eta * eta * fmaxf(0.f, 1.f - cos_i * cos_i);
+                if (!(sin_t2 >= 1.f)) {                                      // TIR guard, tracer.cpp:100-104
+                    float cos_t = sqrtf(1.f - sin_t2);
+                    float kk = eta * cos_i - cos_t;
+                    td = normalized(mk(fmaf(kk, h.n.x, eta * I.x), fmaf(kk, h.n.y, eta * I.y), fmaf(kk, h.n.z, eta * I.z)));
+                    to = h.front ? madd(p, h.n, -1e-6f) : madd(p, h.n, 1e-6f);
+                    want_t = true;
+                }
+            }
+            if (want_r || want_t) {
+                float4* f = frames + 3 * sp;
+                const float owed = want_t && want_r ? kt : 0.f;
+                if (want_r) {                                                // tracer.cpp:38-48
+                    float two = 2.f * dot(I, h.n);
+                    V3 rd = normalized(mk(fmaf(-two, h.n.x, I.x), fmaf(-two, h.n.y, I.y), fmaf(-two, h.n.z, I.z)));
+                    V3 ro = h.front ? madd(p, h.n, 1e-6f) : madd(p, h.n, -1e-6f);
+                    f[0] = make_float4(total.r, total.g, total.b, kr);
+                    f[1] = make_float4(owed, to.x, to.y, to.z);
+                    if (want_t) f[2] = make_float4(td.x, td.y, td.z, 0.f);
+                    o = ro; d = rd;
+                } else {
+                    f[0] = make_float4(total.r, total.g, total.b, kt);
+                    f[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    o = to; d = td;
+                }
+                ++sp;
+                return false;                                                // descend
+            }
+        }
+    }
+    // ---- return `result` to the pending parents ----
+    for (;;) {
+        if (sp == 0) return true;
+        float4* f = frames + 3 * (sp - 1);
+        const float4 f0 = f[0], f1 = f[1];
+        const float k = f0.w;
+        const RGBf total = screen(rgb(f0.x, f0.y, f0.z), rgb(result.r * k, result.g * k, result.b * k));   // tracer.cpp:47,66
+        if (f1.x > 0.f) {                      // reflection done, refraction owed: trace it at depth sp (frame stays)
+            const float4 f2 = f[2];
+            f[0] = make_float4(total.r, total.g, total.b, f1.x);
+            f[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+            o = mk(f1.y, f1.z, f1.w); d = mk(f2.x, f2.y, f2.z);
+            return false;
+        }
+        result = total;
+        --sp;
+    }
+}
+
 }  // namespace rtd

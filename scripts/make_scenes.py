@@ -192,6 +192,7 @@ def main() -> None:
     dump("synthetic_a_tiny.json", synthetic_a(45, n_spheres=120, n_pokeballs=16, n_csg=8, recursion=5))  # CPU-test sized
     dump("synthetic_b_16k.json", synthetic_b(4096))         # 16384x16384, recursion 6
     dump("synthetic_b_4k.json", synthetic_b(1024))          # 4096x4096 single-GPU sized
+    dump("synthetic_b_1k.json", synthetic_b(256))          # 1024x1024, same scene: profiling size
     dump("synthetic_b_small.json", synthetic_b(48))         # 192x192
     dump("quirks.json", quirks())
     print("scenes written to", OUT)

@@ -122,6 +122,37 @@ def test_render_is_deterministic_and_device_path_matches(gpu):
     assert st["primary_rays"] == sc.width * sc.height * 8 and st["kernel_ms"] > 0
 
 
+@pytest.mark.parametrize("name", ["quirks", "synthetic_b_small", "snorlax_4k_reflect_small", "pokeballs_small"])
+def test_wavefront_and_per_thread_kernels_agree(gpu, name, monkeypatch):
+    """Scenes with deep ray trees run the CTA-wavefront kernel, the others one sample per thread; forced either way
+    (RT_FORCE_WAVEFRONT is read at upload) the two must produce the same frame bit for bit, ids included."""
+    out = {}
+    for force in ("0", "1"):
+        monkeypatch.setenv("RT_FORCE_WAVEFRONT", force)
+        sc = gpu.load_scene_from_json(scene_path(name))
+        out[force], tr = render_gpu(gpu, sc, "standard")
+        out[force + "stats"] = tr.last_stats
+        sc.close()
+    for k in ("rgb8", "fb", "ids"):
+        assert np.array_equal(out["0"][k], out["1"][k]), k
+    for k in ("primary_rays", "shadow_rays", "secondary_rays", "prim_tests"):
+        assert out["0stats"][k] == out["1stats"][k], k
+
+
+def test_every_scene_data_path_agrees(gpu, monkeypatch):
+    """RT_FORCE_GLOBAL: the scene read through the global read-only path instead of the staged shared-memory image."""
+    ref = None
+    for force in ("0", "1"):
+        monkeypatch.setenv("RT_FORCE_GLOBAL", force)
+        sc = gpu.load_scene_from_json(scene_path("synthetic_a_tiny"))
+        got, _ = render_gpu(gpu, sc, "standard")
+        sc.close()
+        if ref is None:
+            ref = got
+        else:
+            assert np.array_equal(ref["rgb8"], got["rgb8"]) and np.array_equal(ref["ids"], got["ids"])
+
+
 def test_global_memory_scene_path(gpu, oa):
     """A scene too large for the per-CTA shared-memory image takes the global read-only path."""
     rng = np.random.default_rng(7)
