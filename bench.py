@@ -235,12 +235,30 @@ def run_ours(args) -> None:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def step():
-        tracer.render_device(frame.data_ptr(), stream=stream, rank=rank, world=world)
+    # N > 1: every rank's kernel stores its tiles straight into ONE frame in rank 0's HBM (NVLink peer memory,
+    # sharding.PeerFrame); the NCCL pack/gather/scatter path remains for boxes where the mapping is refused.
+    peer = None
+    if world > 1 and args.exchange == "peer":
+        try:
+            peer = sharding.PeerFrame(rt, W, H, rank, world, dev)
+        except RuntimeError as e:
+            if rank == 0:
+                print("bench.py: %s; using the NCCL gather" % e, file=sys.stderr)
+    target = peer.ptr if peer is not None else frame.data_ptr()
+    exchange = "none (1 GPU)" if world == 1 else "peer stores into rank 0's frame over NVLink + 4-byte all-reduce" if peer is not None else "NCCL gather of owned pixels"
+
+    def finish():
+        if peer is not None:
+            peer.complete()
+            return peer.tensor()
         return sharding.gather_frame(frame, W, H, int(mode), rank, world, index_cache=cache)
 
+    def step():
+        tracer.render_device(target, stream=stream, rank=rank, world=world)
+        return finish()
+
     # rays per frame (deterministic): one untimed render with the device counters read back
-    st = dict(tracer.render_device(frame.data_ptr(), stream=stream, rank=rank, world=world, want_stats=True))
+    st = dict(tracer.render_device(target, stream=stream, rank=rank, world=world, want_stats=True))
     keys = ("primary_rays", "shadow_rays", "secondary_rays", "prim_tests")
     cnt = torch.tensor([st[k] for k in keys], dtype=torch.int64, device=dev)
     if world > 1:
@@ -260,9 +278,9 @@ def run_ours(args) -> None:
     for a, k, b in ev:
         flush.zero_()
         a.record()
-        tracer.render_device(frame.data_ptr(), stream=stream, rank=rank, world=world)
+        tracer.render_device(target, stream=stream, rank=rank, world=world)
         k.record()
-        sharding.gather_frame(frame, W, H, int(mode), rank, world, index_cache=cache)
+        finish()
         b.record()
     barrier()
     clocks = sampler.stop() if rank == 0 else {}
@@ -285,8 +303,8 @@ def run_ours(args) -> None:
             st2 = rt.RtStats()
             rt._check(rt.lib().rt_render(s2.device_handle(), int(mode), 0, 1, C.c_void_p(host.data_ptr()), None, None, C.byref(st2)))
         else:
-            t2.render_device(frame.data_ptr(), stream=stream, rank=rank, world=world)
-            full = sharding.gather_frame(frame, W, H, int(mode), rank, world, index_cache=cache)
+            t2.render_device(target, stream=stream, rank=rank, world=world)
+            full = finish()
             if rank == 0:
                 host.copy_(full, non_blocking=True)
             torch.cuda.synchronize()
@@ -311,7 +329,7 @@ def run_ours(args) -> None:
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": os.path.basename(args.scene), "width": W, "height": H, "spp": 1 if args.paper else 8,
                        "mode": "paper" if args.paper else "standard", "recursion": int(d.recursion), "lights": int(d.n_lights),
-                       "objects": int(d.n_objects), "csg_leaves": int(d.n_leaves), "parallelism": f"row-tile interleave x{world}",
+                       "objects": int(d.n_objects), "csg_leaves": int(d.n_leaves), "parallelism": f"row-tile interleave x{world}", "exchange": exchange,
                        "l2": "flushed between timed steps (256 MB memset)"},
             "rays_per_frame": rays_per_frame, "rays": tot, "kernel_ms": kernel_ms,
             "e2e": {"value": rays_per_frame / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_frame": e2e_ms,
@@ -336,6 +354,8 @@ def run_ours(args) -> None:
             except Exception as e:  # the baseline is a report, never a reason to lose the GPU number
                 line["cpu_baseline"] = {"error": str(e)}
         print(json.dumps(line))
+    if peer is not None:
+        peer.close()
     if world > 1:
         dist.destroy_process_group()
 
@@ -348,6 +368,7 @@ def main() -> None:
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--scene", default=DEFAULT_SCENE)
     ap.add_argument("--paper", action="store_true")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "gather"], help="N>1: how pixels reach rank 0")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     args = ap.parse_args()

@@ -179,6 +179,20 @@ int rt_render_device(rt_scene*, int mode, int rank, int world,
                      void* rgba8_device, void* rgbf_device, void* ids_device,
                      void* stream, rt_stats* stats);
 
+/* ---- peer frame (multi-GPU, one process per GPU) ---------------------------------------------------
+ * The reference writes one std::vector<Color> (tracer.cpp:250,297); with several GPUs the ranks write their
+ * tiles straight into ONE RGBA8 frame that lives on rank 0, over NVLink peer memory, so the render kernel's
+ * pixel store is also the "gather" and no collective moves pixels afterwards:
+ *   rank 0      : rt_peer_frame_create(bytes, &ptr, handle)   (zero-filled device allocation + 64-byte IPC handle)
+ *   other ranks : rt_peer_frame_open(handle, &ptr)            (maps rank 0's allocation, enables peer access)
+ *   every rank  : rt_render_device(scene, mode, rank, world, ptr, ...), then any stream-ordered barrier
+ *   at the end  : rt_peer_frame_close(ptr, is_owner)
+ * The handle is plain bytes and travels over whatever channel the host has (torch.distributed here).     */
+#define RT_IPC_HANDLE_BYTES 64
+int rt_peer_frame_create(size_t bytes, void** device_ptr, unsigned char handle[RT_IPC_HANDLE_BYTES]);
+int rt_peer_frame_open(const unsigned char handle[RT_IPC_HANDLE_BYTES], void** device_ptr);
+int rt_peer_frame_close(void* device_ptr, int is_owner);
+
 /* Known-answer entry point: trace n arbitrary rays (6 doubles each: origin, direction) through
  * Scene::intersect(1e-4, inf) + Tracer::trace; out = 16 doubles per ray:
  *   hit, t, p[3], n[3], front_face, code, r, g, b, occluded on (1e-3, 5], 2 pad.                  */

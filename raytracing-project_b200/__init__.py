@@ -93,6 +93,7 @@ ABI_SYMBOLS = [
     "rt_render", "rt_render_device", "rt_trace_rays", "rt_debug_jitter", "rt_debug_mt_block_host", "rt_debug_device_layout",
     "rt_measure_fp32_peak",
     "rt_write_png_rgb8",
+    "rt_peer_frame_create", "rt_peer_frame_open", "rt_peer_frame_close",
 ]
 
 _lib = None
@@ -130,6 +131,9 @@ def lib():
         L.rt_measure_fp32_peak.argtypes = [C.POINTER(C.c_double)]
         L.rt_debug_device_layout.argtypes = [C.POINTER(RtSceneDesc), C.c_void_p, C.POINTER(C.c_int), C.c_void_p, C.POINTER(C.c_int), C.c_void_p]
         L.rt_write_png_rgb8.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_int]
+        L.rt_peer_frame_create.argtypes = [C.c_size_t, C.POINTER(C.c_void_p), C.c_char_p]
+        L.rt_peer_frame_open.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
+        L.rt_peer_frame_close.argtypes = [C.c_void_p, C.c_int]
         _lib = L
     return _lib
 
@@ -277,6 +281,30 @@ def measure_fp32_peak() -> float:
     v = C.c_double()
     _check(lib().rt_measure_fp32_peak(C.byref(v)))
     return float(v.value)
+
+
+IPC_HANDLE_BYTES = 64
+
+
+def peer_frame_create(nbytes: int):
+    """Zero-filled device allocation that other processes can map (rank 0 of a multi-GPU frame): (ptr, handle bytes)."""
+    ptr = C.c_void_p()
+    h = C.create_string_buffer(IPC_HANDLE_BYTES)
+    _check(lib().rt_peer_frame_create(nbytes, C.byref(ptr), h))
+    return int(ptr.value), h.raw
+
+
+def peer_frame_open(handle: bytes) -> int:
+    """Map another rank's peer frame into this process (NVLink peer memory); returns the device pointer."""
+    if len(handle) != IPC_HANDLE_BYTES:
+        raise ValueError("IPC handle must be %d bytes" % IPC_HANDLE_BYTES)
+    ptr = C.c_void_p()
+    _check(lib().rt_peer_frame_open(C.create_string_buffer(handle, IPC_HANDLE_BYTES), C.byref(ptr)))
+    return int(ptr.value)
+
+
+def peer_frame_close(ptr: int, owner: bool) -> None:
+    _check(lib().rt_peer_frame_close(C.c_void_p(ptr), 1 if owner else 0))
 
 
 def write_png_rgb8(path: str, rgb8: np.ndarray) -> None:

@@ -495,6 +495,47 @@ int rt_render_device(rt_scene* s, int mode, int rank, int world, void* rgba8_dev
     return RT_OK;
 }
 
+int rt_peer_frame_create(size_t bytes, void** device_ptr, unsigned char handle[RT_IPC_HANDLE_BYTES]) {
+    static_assert(sizeof(cudaIpcMemHandle_t) == RT_IPC_HANDLE_BYTES, "IPC handle size");
+    if (!device_ptr || !handle || bytes == 0) return fail(RT_ERR_ARG, "rt_peer_frame_create: null argument or zero size");
+    if (!g_ctx.ready) return fail(RT_ERR_STATE, "rt_peer_frame_create: rt_init has not been called");
+    std::lock_guard<std::mutex> lk(g_ctx.mu);
+    CU(cudaSetDevice(g_ctx.device));
+    void* p = nullptr;
+    CU(cudaMalloc(&p, bytes));
+    CU(cudaMemset(p, 0, bytes));
+    cudaIpcMemHandle_t h;
+    cudaError_t e = cudaIpcGetMemHandle(&h, p);
+    if (e != cudaSuccess) { cudaFree(p); return fail(RT_ERR_CUDA, std::string("cudaIpcGetMemHandle: ") + cudaGetErrorString(e)); }
+    std::memcpy(handle, &h, sizeof h);
+    *device_ptr = p;
+    return RT_OK;
+}
+
+int rt_peer_frame_open(const unsigned char handle[RT_IPC_HANDLE_BYTES], void** device_ptr) {
+    if (!device_ptr || !handle) return fail(RT_ERR_ARG, "rt_peer_frame_open: null argument");
+    if (!g_ctx.ready) return fail(RT_ERR_STATE, "rt_peer_frame_open: rt_init has not been called");
+    std::lock_guard<std::mutex> lk(g_ctx.mu);
+    CU(cudaSetDevice(g_ctx.device));
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle, sizeof h);
+    void* p = nullptr;
+    cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) { (void)cudaGetLastError(); return fail(RT_ERR_CUDA, std::string("cudaIpcOpenMemHandle: ") + cudaGetErrorString(e)); }
+    *device_ptr = p;
+    return RT_OK;
+}
+
+int rt_peer_frame_close(void* device_ptr, int is_owner) {
+    if (!device_ptr) return RT_OK;
+    if (!g_ctx.ready) return fail(RT_ERR_STATE, "rt_peer_frame_close: rt_init has not been called");
+    std::lock_guard<std::mutex> lk(g_ctx.mu);
+    CU(cudaSetDevice(g_ctx.device));
+    CU(cudaDeviceSynchronize());
+    if (is_owner) CU(cudaFree(device_ptr)); else CU(cudaIpcCloseMemHandle(device_ptr));
+    return RT_OK;
+}
+
 int rt_render(rt_scene* s, int mode, int rank, int world, uint8_t* rgb8, float* rgbf, int32_t* ids, rt_stats* stats) {
     int rc = check_args(s, mode, rank, world); if (rc) return rc;
     std::lock_guard<std::mutex> lk(g_ctx.mu);

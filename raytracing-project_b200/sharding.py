@@ -9,9 +9,17 @@ stream is known, so the frame shards with NO data-path collecti
 * Paper mode: blocks of 16 image rows, interleaved; the 1-row halo of the edge detector
   (tracer.cpp:133-178) is recomputed locally.
 
-The only exchange is the gather of each rank's finished RGBA8 pixels to rank 0
-(`gather_frame`): NCCL over NVLink on GPUs, gloo on CPU for the tests.  This module is pure
-index arithmetic + torch.distributed plumbing; it launches no kernels of its own.
+The only exchange is getting each rank's finished RGBA8 pixels to rank 0.  Two ways:
+
+* `PeerFrame` (GPUs): ONE frame allocated on rank 0 and mapped into every other process through a
+  CUDA IPC handle (include/rt_b200.h, rt_peer_frame_*).  Every rank passes that pointer to
+  rt_render_device, so the render kernel's own pixel store lands in rank 0's HBM over NVLink and
+  nothing is moved afterwards; `complete()` is a stream-ordered 4-byte all-reduce that tells rank 0
+  every peer's kernel has retired.
+* `gather_frame`: pack owned pixels, NCCL/gloo gather, scatter on rank 0.  Used by the CPU (gloo)
+  tests and as the path when peer mapping is not available on a box.
+
+This module is index arithmetic + torch.distributed plumbing; it launches no kernels of its own.
 """
 from __future__ import annotations
 
@@ -71,3 +79,78 @@ def gather_frame(local_rgba, width: int, height: int, mode: int, rank: int, worl
         return out.view(torch.uint8).view(height, width, 4)
     dist.gather(mine, None, dst=0, group=group)
     return None
+
+
+class PeerFrame:
+    """An [H, W, 4] uint8 frame in rank 0's HBM that every rank renders into directly (NVLink peer stores).
+
+    `ptr` is what each rank passes to Tracer.render_device as the RGBA8 target.  Ranks write disjoint
+    pixels (`owned_pixels`), so there is no ordering between them; `complete()` orders rank 0's readers
+    after every rank's kernel.  Collective: construct, `complete()` and `close()` on all ranks."""
+
+    def __init__(self, rt, width: int, height: int, rank: int, world: int, device, group=None):
+        import torch
+        import torch.distributed as dist
+
+        self.rt, self.rank, self.world, self.group = rt, rank, world, group
+        self.width, self.height, self.device = width, height, device
+        self.ptr = 0
+        self.owner = rank == 0
+        box = torch.zeros(rt.IPC_HANDLE_BYTES, dtype=torch.uint8, device=device)
+        ok = torch.ones(1, dtype=torch.int32, device=device)
+        err = None
+        if self.owner:
+            try:
+                self.ptr, handle = rt.peer_frame_create(width * height * 4)
+                box.copy_(torch.frombuffer(bytearray(handle), dtype=torch.uint8))
+            except Exception as e:          # noqa: BLE001 - reported below, collectively
+                err = e; ok.zero_()
+        if world > 1:
+            dist.broadcast(box, src=0, group=group)
+        if not self.owner:
+            try:
+                self.ptr = rt.peer_frame_open(bytes(box.cpu().numpy().tobytes()))
+            except Exception as e:          # noqa: BLE001
+                err = e; ok.zero_()
+        if world > 1:
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+        self._flag = torch.zeros(1, dtype=torch.int32, device=device)
+        if int(ok.item()) == 0:
+            self.close()
+            raise RuntimeError("peer frame unavailable on this box: %s" % (err if err is not None else "another rank failed to map it"))
+
+    @property
+    def __cuda_array_interface__(self):
+        return {"shape": (self.height, self.width, 4), "typestr": "|u1", "data": (self.ptr, False), "version": 2}
+
+    def tensor(self):
+        """The assembled frame as a torch tensor (rank 0 only; valid after `complete()`)."""
+        import torch
+
+        if not self.owner:
+            return None
+        return torch.as_tensor(self, device=self.device)
+
+    def complete(self) -> None:
+        """Stream-ordered: after this, work queued on rank 0's current stream sees every rank's pixels."""
+        import torch.distributed as dist
+
+        if self.world > 1:
+            dist.all_reduce(self._flag, group=self.group)
+
+    def close(self) -> None:
+        import torch
+        import torch.distributed as dist
+
+        multi = self.world > 1 and dist.is_initialized()
+        if multi:
+            torch.cuda.synchronize()
+            dist.barrier(group=self.group)          # nobody unmaps while a peer kernel may still store
+        if self.ptr and not self.owner:
+            self.rt.peer_frame_close(self.ptr, False)
+            self.ptr = 0
+        if multi:
+            dist.barrier(group=self.group)          # the owner frees only after every mapping is gone
+        if self.ptr:
+            self.rt.peer_frame_close(self.ptr, True)
+            self.ptr = 0

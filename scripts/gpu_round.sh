@@ -19,7 +19,7 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-fil
     python bench.py --steps 2 --warmup 3 --no-cpu > $OUT/ncu_bench.log 2>&1
 for sc in snorlax_4k synthetic_a_2k synthetic_b_small; do
 python scripts/profile_run.py scenes/$sc.json standard 2 > $OUT/plain_prof_$sc.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:render_standard -s 1 -c 1 -o $OUT/prof_$sc \
+ncu --set full --clock-control none --import-source on -k "regex:render_(standard|wavefront)" -s 1 -c 1 -o $OUT/prof_$sc \
     python scripts/profile_run.py scenes/$sc.json standard 2 > $OUT/ncu_prof_$sc.log 2>&1
 done
 python scripts/profile_run.py scenes/penguin_4k.json paper 2 > $OUT/plain_prof_paper.log 2>&1 &&
