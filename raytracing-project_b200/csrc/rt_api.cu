@@ -53,6 +53,8 @@ template <class T> int upload(const std::vector<T>& h, T** d) {
 struct rt_scene {
     rtd::SceneHeader hdr{};
     bool fits_const{false};   // scanned arrays fit the shared-memory budget (staged per CTA)
+    bool flat{false};         // no ray can spawn a child (no reflective / refractive material, or recursion == 1)
+    bool lockstep{false};     // flat scene with generic objects (CSG programs, wrapped primitives): see trace_flat
     bool bounces{false};      // most materials reflect or refract and medium.recursion >= 2: deep, uneven ray trees
     size_t smem_bytes{0};
     std::vector<float4> obj_geom, leaf_geom, pokeballs, affines, materials, lights, fallbacks, clusters;
@@ -241,8 +243,10 @@ int rt_init(int device) {
     uint32_t seed[mt::kN]; mt::seed_state(12345u, seed);                  // tracer.cpp:284
     CU(cudaMemcpy(g_ctx.mt_resume, seed, sizeof(seed), cudaMemcpyHostToDevice));
     g_ctx.mt_tiles = 0; g_ctx.mt_capacity = 0; g_ctx.mt_table = nullptr; g_ctx.const_owner = nullptr;
-    CU(cudaFuncSetAttribute(rtd::render_standard_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget));
-    CU(cudaFuncSetAttribute(rtd::render_standard_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget));
+    CU(cudaFuncSetAttribute(rtd::render_standard_kernel<true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget));
+    CU(cudaFuncSetAttribute(rtd::render_standard_kernel<true, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget));
+    CU(cudaFuncSetAttribute(rtd::render_standard_kernel<true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget));
+    CU(cudaFuncSetAttribute(rtd::render_standard_kernel<true, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget));
     CU(cudaFuncSetAttribute(rtd::render_wavefront_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget));
     CU(cudaFuncSetAttribute(rtd::render_wavefront_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget));
     CU(cudaFuncSetAttribute(rtd::paper_gbuffer_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget));
@@ -305,6 +309,10 @@ int rt_scene_upload(const rt_scene_desc* d, rt_scene** out) {
     // whose ray trees are mostly depth 1 (snorlax with one reflective sphere), and gains ~6 % on the all-glass lattice.
     int n_bounce = 0;
     for (int i = 0; i < d->n_materials; ++i) n_bounce += (d->materials[i].kr > 0.f || d->materials[i].kt > 0.f) ? 1 : 0;
+    s->flat = d->recursion >= 1 && (n_bounce == 0 || d->recursion == 1);
+    if (const char* e = std::getenv("RT_FORCE_FLAT")) if (e[0] == '0') s->flat = false;            // test hook: generic loop on a flat scene
+    s->lockstep = s->flat && (d->n_ops > 0 || d->n_affines > 0);
+    if (const char* e = std::getenv("RT_FORCE_LOCKSTEP")) s->lockstep = s->flat && e[0] == '1';     // test hook
     s->bounces = d->recursion >= 2 && d->n_materials > 0 && 2 * n_bounce >= d->n_materials;
     if (const char* e = std::getenv("RT_FORCE_WAVEFRONT")) s->bounces = e[0] == '1';       // test hook: either kernel on any scene
     if (const char* e = std::getenv("RT_FORCE_GLOBAL")) if (e[0] == '1') s->fits_const = false;   // test hook: exercise the global-memory path on any scene
@@ -418,18 +426,21 @@ int launch_frame(rt_scene* s, int mode, int rank, int world, uchar4* rgba8, floa
     rtd::RenderParams prm{};
     prm.mt_table = g_ctx.mt_table; prm.rgba8 = rgba8; prm.rgbf = rgbf; prm.ids = ids;
     prm.counters = g_ctx.counters; prm.tile_counter = g_ctx.tile_counter;
-    prm.n_local_tiles = (int)local; prm.rank = rank; prm.world = world; prm.n_pixels = npx;
+    prm.n_local_tiles = (int)local; prm.rank = rank; prm.world = world; prm.n_pixels = npx; prm.lockstep = s->lockstep ? 1 : 0;
     CU(cudaMemsetAsync(g_ctx.tile_counter, 0, sizeof(unsigned), st));
     // kernel variant: <scene staged in shared memory, scene has bounds>; ray trees deeper than 1 -> wavefront kernel
     const bool kk = !s->clusters.empty();
     auto kernel = s->bounces
         ? (s->fits_const ? (kk ? rtd::render_wavefront_kernel<true, true> : rtd::render_wavefront_kernel<true, false>)
                          : (kk ? rtd::render_wavefront_kernel<false, true> : rtd::render_wavefront_kernel<false, false>))
-        : (s->fits_const ? (kk ? rtd::render_standard_kernel<true, true> : rtd::render_standard_kernel<true, false>)
-                         : (kk ? rtd::render_standard_kernel<false, true> : rtd::render_standard_kernel<false, false>));
+        : s->flat ? (s->fits_const ? (kk ? rtd::render_standard_kernel<true, true, true> : rtd::render_standard_kernel<true, false, true>)
+                                   : (kk ? rtd::render_standard_kernel<false, true, true> : rtd::render_standard_kernel<false, false, true>))
+                  : (s->fits_const ? (kk ? rtd::render_standard_kernel<true, true, false> : rtd::render_standard_kernel<true, false, false>)
+                                   : (kk ? rtd::render_standard_kernel<false, true, false> : rtd::render_standard_kernel<false, false, false>));
     const size_t smem = s->fits_const ? s->smem_bytes : 0;
     int per_sm = 0;
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, rtd::kRenderThreads, smem));
+    const int threads = rtd::kRenderThreads;
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem));
     const long long units = s->bounces ? (local + rtd::kWaveTiles - 1) / rtd::kWaveTiles : local;      // the wavefront kernel takes tiles in batches
     const long long grid = std::max<long long>(1, std::min<long long>(units, (long long)g_ctx.sms * std::max(per_sm, 1)));
     if (s->bounces) {
@@ -438,7 +449,7 @@ int launch_frame(rt_scene* s, int mode, int rank, int world, uchar4* rgba8, floa
         prm.wave_state = g_ctx.d_wave;
     }
     if (local > 0) {
-        kernel<<<(unsigned)grid, rtd::kRenderThreads, smem, st>>>(prm);
+        kernel<<<(unsigned)grid, threads, smem, st>>>(prm);
         CU(cudaGetLastError());
     }
     if (n_tiles_out) *n_tiles_out = (int)local;

@@ -71,6 +71,7 @@ struct RenderParams {
     unsigned* tile_counter;       // dynamic tile scheduler
     float4* wave_state;           // wavefront kernel: per CTA, per sample of its tile: ray + pending parents
     int n_local_tiles, rank, world;
+    int lockstep;                 // flat scenes: CTA barrier before every light (trace_flat)
     long long n_pixels;
 };
 
@@ -108,10 +109,11 @@ __device__ __forceinline__ void flush_counters(const Counters& c, unsigned long 
 #endif
 constexpr int kRenderThreads = 256;
 
-template <bool C, bool K>
+// F ("flat"): no ray of the scene can spawn a child, see trace_flat.
+template <bool C, bool K, bool F>
 __global__ void __launch_bounds__(kRenderThreads, RT_MIN_BLOCKS) render_standard_kernel(RenderParams prm) {
-    __shared__ uint32_t st[2][mt::kN];
-    __shared__ __align__(16) uint32_t outw[mt::kOutputsPerTile];
+    // raw generator words: [0, kN) the tile's checkpoint, then the 8 blocks it yields (tempered on use)
+    __shared__ __align__(16) uint32_t raw[mt::kN + mt::kOutputsPerTile];
     __shared__ int s_tile;
     const int tid = threadIdx.x;
     const int nx = c_hdr.nx, ny = c_hdr.ny;
@@ -124,17 +126,12 @@ __global__ void __launch_bounds__(kRenderThreads, RT_MIN_BLOCKS) render_standard
         if (local >= prm.n_local_tiles) break;
         const long long tile = (long long)prm.rank + (long long)local * prm.world;
         // --- the tile's 4992 raw outputs: checkpoint + 8 twists (one barrier each) ---
-        for (int k = tid; k < mt::kN; k += kRenderThreads) st[0][k] = __ldg(prm.mt_table + tile * mt::kN + k);
+        for (int k = tid; k < mt::kN; k += kRenderThreads) raw[k] = __ldg(prm.mt_table + tile * mt::kN + k);
         __syncthreads();
-        int cur = 0;
 #pragma unroll 1
         for (int b = 0; b < mt::kTwistsPerTile; ++b) {
-            for (int k = tid; k < mt::kN; k += kRenderThreads) {
-                uint32_t w = mt::next_word(st[cur], k);
-                st[cur ^ 1][k] = w; outw[b * mt::kN + k] = mt::temper(w);
-            }
+            for (int k = tid; k < mt::kN; k += kRenderThreads) raw[(b + 1) * mt::kN + k] = mt::next_word(raw + b * mt::kN, k);
             __syncthreads();
-            cur ^= 1;
         }
         // --- one sample per thread; 8 consecutive lanes share a pixel ---
         const long long pix0 = tile * mt::kPixelsPerTile;
@@ -145,15 +142,20 @@ __global__ void __launch_bounds__(kRenderThreads, RT_MIN_BLOCKS) render_standard
             const bool active = j < mt::kSamplesPerTile && p < prm.n_pixels;
             RGBf c = rgb(0.f, 0.f, 0.f);
             int x = 0, yy = 0;
+            V3 o = mk(0.f, 0.f, 0.f), d = mk(0.f, 1.f, 0.f);
             if (active) {
                 const int y = (int)(p / nx); x = (int)(p - (long long)y * nx); yy = ny - 1 - y;   // row flip on store (tracer.cpp:297)
-                const uint4 w = *reinterpret_cast<const uint4*>(outw + 4 * j);
+                uint4 w = *reinterpret_cast<const uint4*>(raw + mt::kN + 4 * j);
+                w.x = mt::temper(w.x); w.y = mt::temper(w.y); w.z = mt::temper(w.z); w.w = mt::temper(w.w);
                 const double jx = mt::jitter(w.x, w.y), jy = mt::jitter(w.z, w.w);              // dx first (tracer.cpp:293)
                 const double sx = ((double)x + 0.5 + jx) / (double)nx, sy = ((double)y + 0.5 + jy) / (double)ny;
-                V3 o, d; camera_ray(sx, sy, o, d);
+                camera_ray(sx, sy, o, d);
+            }
+            if (F || active) {
                 Hit ph; bool phit;
-                c = trace<C, K>(o, d, &ph, &phit, cnt);
-                if (prm.ids) prm.ids[((long long)yy * nx + x) * 8 + (j & 7)] = phit ? ph.code : -1;
+                if (F) { c = trace_flat<C, K>(active, prm.lockstep != 0, o, d, ph, phit, cnt); if (!active) c = rgb(0.f, 0.f, 0.f); }
+                else c = trace<C, K>(o, d, &ph, &phit, cnt);
+                if (active && prm.ids) prm.ids[((long long)yy * nx + x) * 8 + (j & 7)] = phit ? ph.code : -1;
             }
 #pragma unroll
             for (int off = 1; off < 8; off <<= 1) {
@@ -168,7 +170,7 @@ __global__ void __launch_bounds__(kRenderThreads, RT_MIN_BLOCKS) render_standard
                 if (prm.rgbf) prm.rgbf[q] = make_float4(c.r, c.g, c.b, 1.f);
             }
         }
-        __syncthreads();           // outw / s_tile reuse
+        __syncthreads();           // raw / s_tile reuse
     }
     flush_counters(cnt, prm.counters);
 }

@@ -57,12 +57,11 @@ __device__ bool generic_hit(int i, V3 o, V3 d, float tmin, float tmax, float& t_
 }
 
 // ---- Scene::intersect (scene.cpp:10-24) ------------------------------------------------------------------
+// One run of the object list against the best hit so far.
 template <bool C, bool K>
-__device__ bool closest_hit(V3 o, V3 d, float tmin, float tmax, Hit& hit, Counters& cnt) {
-    int best = -1; float best_t = tmax; uint32_t best_code = 0; float best_tent = 0.f;
-    const int n_runs = c_hdr.n_runs;
-    for (int r = 0; r < n_runs; ++r) {
-        const int4 run = SV<C>::run(r);
+__device__ __forceinline__ void run_closest(const int4 run, V3 o, V3 d, float tmin, int& best, float& best_t, uint32_t& best_code,
+                                            float& best_tent, Counters& cnt) {
+    {
         const int first = run.y, end = run.y + run.z;
         if (K && (run.x == RUN_SPHERE || run.x == RUN_POKEBALL) && run.w > 0) {
             // Clustered run (spatially reordered, 16 primitives per cluster): candidate mask over the cluster bounds,
@@ -124,6 +123,13 @@ __device__ bool closest_hit(V3 o, V3 d, float tmin, float tmax, Hit& hit, Counte
             }
         }
     }
+}
+
+template <bool C, bool K>
+__device__ bool closest_hit(V3 o, V3 d, float tmin, float tmax, Hit& hit, Counters& cnt) {
+    int best = -1; float best_t = tmax; uint32_t best_code = 0; float best_tent = 0.f;
+    const int n_runs = c_hdr.n_runs;
+    for (int r = 0; r < n_runs; ++r) run_closest<C, K>(SV<C>::run(r), o, d, tmin, best, best_t, best_code, best_tent, cnt);
     if (best < 0) return false;
     // ---- finalise the winner: normal, front_face, material, id code ----
     const int4 m = SV<C>::obj_meta(best);
@@ -164,10 +170,8 @@ __device__ bool closest_hit(V3 o, V3 d, float tmin, float tmax, Hit& hit, Counte
 
 // ---- Scene::occluded (scene.cpp:33-42) ---------------------------------------------------------------------
 template <bool C, bool K>
-__device__ bool occluded(V3 o, V3 d, float tmin, float tmax, Counters& cnt) {
-    const int n_runs = c_hdr.n_runs;
-    for (int r = 0; r < n_runs; ++r) {
-        const int4 run = SV<C>::run(r);
+__device__ __forceinline__ bool run_occludes(const int4 run, V3 o, V3 d, float tmin, float tmax, Counters& cnt) {
+    {
         const int first = run.y, end = run.y + run.z;
         if (K && (run.x == RUN_SPHERE || run.x == RUN_POKEBALL) && run.w > 0) {     // clustered run (see closest_hit)
             const int ctab = run.w - 1, ncl = (run.z + 15) >> 4;
@@ -227,6 +231,14 @@ __device__ bool occluded(V3 o, V3 d, float tmin, float tmax, Counters& cnt) {
     return false;
 }
 
+template <bool C, bool K>
+__device__ bool occluded(V3 o, V3 d, float tmin, float tmax, Counters& cnt) {
+    const int n_runs = c_hdr.n_runs;
+    for (int r = 0; r < n_runs; ++r)
+        if (run_occludes<C, K>(SV<C>::run(r), o, d, tmin, tmax, cnt)) return true;
+    return false;
+}
+
 // ---- shade_lambert_phong (shading.cpp:31-138) ------------------------------------------------------------------
 struct RGBf { float r, g, b; };
 __device__ __forceinline__ RGBf rgb(float r, float g, float b) { RGBf c; c.r = r; c.g = g; c.b = b; return c; }
@@ -234,45 +246,78 @@ __device__ __forceinline__ RGBf rgb(float r, float g, float b) { RGBf c; c.r = r
 __device__ __forceinline__ float screen1(float a, float b) { return 1.f - (1.f - a) * (1.f - b); }
 __device__ __forceinline__ RGBf screen(RGBf a, RGBf b) { return rgb(screen1(a.r, b.r), screen1(a.g, b.g), screen1(a.b, b.b)); }
 
+// One light's contribution, screen-blended into E (shading.cpp:79-130).
+template <bool C, bool K>
+__device__ __forceinline__ void light_term(int l, const float4 m0, float ks, float shininess, float kd, V3 n, V3 p, V3 so, V3 wo,
+                                           float eps, RGBf& E, Counters& cnt) {
+    const float4 lp = SV<C>::light(l, 0), li = SV<C>::light(l, 1);
+    V3 L = mk(lp.x - p.x, lp.y - p.y, lp.z - p.z);
+    float d2 = fmaxf(dot(L, L), 0.01f);
+    float dist = sqrtf(d2);
+    float inv = 1.f / dist;
+    V3 wi = mk(L.x * inv, L.y * inv, L.z * inv);
+    float ndotl = fmaxf(0.f, dot(n, wi));
+    if (ndotl <= 0.f) return;
+    float tmaxS = dist - eps;
+    if (tmaxS <= eps) return;
+    ++cnt.shadow;
+    if (occluded<C, K>(so, normalized(wi), eps, tmaxS, cnt)) return;            // Ray ctor re-normalises (core.h:278)
+    float eff = fmaxf(0.5f, dist);
+    float fall = 2.0f / (eff * eff);                                         // falloff * 2.0 (shading.cpp:108-112)
+    RGBf I = rgb(li.x * fall, li.y * fall, li.z * fall);
+    float kdn = kd * ndotl * 1.5f;                                           // shading.cpp:115
+    RGBf Ed = rgb(m0.x * I.r * kdn, m0.y * I.g * kdn, m0.z * I.b * kdn);
+    RGBf Es = rgb(0.f, 0.f, 0.f);
+    if (ks > 0.f) {                                                          // shading.cpp:118-126
+        float two = 2.f * dot(n, wi);
+        V3 rr = normalized(mk(fmaf(two, n.x, -wi.x), fmaf(two, n.y, -wi.y), fmaf(two, n.z, -wi.z)));
+        float rdotv = fmaxf(0.f, dot(rr, wo));
+        // exp2(s * log2(x)) on the MUFU pipe (relative error ~ s * 2^-21, far below 1/255); x == 0 keeps powf's edge cases
+        float spec = (rdotv > 0.f ? __powf(rdotv, shininess) : powf(rdotv, shininess)) * ks;
+        Es = rgb(I.r * spec, I.g * spec, I.b * spec);
+    }
+    E = screen(E, screen(Ed, Es));
+}
+
 template <bool C, bool K>
 __device__ RGBf shade(const Hit& h, V3 p, V3 wo, Counters& cnt) {
     if (h.mat < 0) return rgb(1.f, 0.f, 1.f);                                // shading.cpp:33
     const float4 m0 = material(h.mat, 0), m1 = material(h.mat, 1), m2 = material(h.mat, 2);
-    const float ks = m0.w, shininess = m2.y, kd = m2.w;
-    const V3 n = h.n;
     RGBf E = rgb(m1.x, m1.y, m1.z);                                          // ambient (x) scene ambient, pre-multiplied
     const float eps = fmaxf(1e-3f, 1e-4f * h.t);                             // shading.cpp:43
-    const V3 so = madd(p, n, eps);
+    const V3 so = madd(p, h.n, eps);
     const int nl = c_hdr.n_lights;
-    for (int l = 0; l < nl; ++l) {                                           // shading.cpp:79-130
-        const float4 lp = SV<C>::light(l, 0), li = SV<C>::light(l, 1);
-        V3 L = mk(lp.x - p.x, lp.y - p.y, lp.z - p.z);
-        float d2 = fmaxf(dot(L, L), 0.01f);
-        float dist = sqrtf(d2);
-        float inv = 1.f / dist;
-        V3 wi = mk(L.x * inv, L.y * inv, L.z * inv);
-        float ndotl = fmaxf(0.f, dot(n, wi));
-        if (ndotl <= 0.f) continue;
-        float tmaxS = dist - eps;
-        if (tmaxS <= eps) continue;
-        ++cnt.shadow;
-        if (occluded<C, K>(so, normalized(wi), eps, tmaxS, cnt)) continue;      // Ray ctor re-normalises (core.h:278)
-        float eff = fmaxf(0.5f, dist);
-        float fall = 2.0f / (eff * eff);                                     // falloff * 2.0 (shading.cpp:108-112)
-        RGBf I = rgb(li.x * fall, li.y * fall, li.z * fall);
-        float kdn = kd * ndotl * 1.5f;                                       // shading.cpp:115
-        RGBf Ed = rgb(m0.x * I.r * kdn, m0.y * I.g * kdn, m0.z * I.b * kdn);
-        RGBf Es = rgb(0.f, 0.f, 0.f);
-        if (ks > 0.f) {                                                      // shading.cpp:118-126
-            float two = 2.f * dot(n, wi);
-            V3 rr = normalized(mk(fmaf(two, n.x, -wi.x), fmaf(two, n.y, -wi.y), fmaf(two, n.z, -wi.z)));
-            float rdotv = fmaxf(0.f, dot(rr, wo));
-            // exp2(s * log2(x)) on the MUFU pipe (relative error ~ s * 2^-21, far below 1/255); x == 0 keeps powf's edge cases
-            float spec = (rdotv > 0.f ? __powf(rdotv, shininess) : powf(rdotv, shininess)) * ks;
-            Es = rgb(I.r * spec, I.g * spec, I.b * spec);
-        }
-        E = screen(E, screen(Ed, Es));
+    for (int l = 0; l < nl; ++l) light_term<C, K>(l, m0, m0.w, m2.y, m2.w, h.n, p, so, wo, eps, E, cnt);
+    return rgb(fminf(1.5f, E.r), fminf(1.5f, E.g), fminf(1.5f, E.b));        // shading.cpp:133-135
+}
+
+// Tracer::trace for a scene in which no ray can spawn a child (no material reflects or refracts, or recursion == 1):
+// one closest hit, one shade, no stack.  Every thread of the CTA calls it, also those without a sample (`active`
+// false).  With `lockstep` the CTA meets at a barrier before every light: warps that walk the same code at the same
+// time share instruction-cache lines, which is what limits this kernel on scenes with CSG programs (snorlax 4K
+// 15.96 -> 14.44 ms); on scenes of a few plain spheres the waiting costs more than it saves (penguin 4K 6.08 -> 6.31 ms),
+// so the flag is set per scene on upload.
+template <bool C, bool K>
+__device__ RGBf trace_flat(bool active, bool lockstep, V3 o, V3 d, Hit& primary, bool& primary_hit, Counters& cnt) {
+    Hit h; h.mat = -1; h.t = 0.f; h.n = mk(0.f, 1.f, 0.f);
+    bool hit = false;
+    if (active) { hit = closest_hit<C, K>(o, d, 1e-4f, kInf, h, cnt); ++cnt.primary; }     // tracer.cpp:29
+    primary = h; primary_hit = hit;
+    const bool lit = hit && h.mat >= 0;
+    const V3 p = madd(o, d, h.t);
+    const V3 wo = normalized(neg(d));
+    float4 m0 = make_float4(0.f, 0.f, 0.f, 0.f), m1 = m0, m2 = m0;
+    if (lit) { m0 = material(h.mat, 0); m1 = material(h.mat, 1); m2 = material(h.mat, 2); }
+    RGBf E = rgb(m1.x, m1.y, m1.z);
+    const float eps = fmaxf(1e-3f, 1e-4f * h.t);
+    const V3 so = madd(p, h.n, eps);
+    const int nl = c_hdr.n_lights;
+    for (int l = 0; l < nl; ++l) {
+        if (lockstep) __syncthreads();
+        if (lit) light_term<C, K>(l, m0, m0.w, m2.y, m2.w, h.n, p, so, wo, eps, E, cnt);
     }
+    if (!hit) return rgb(c_hdr.bg[0], c_hdr.bg[1], c_hdr.bg[2]);             // tracer.cpp:72
+    if (!lit) return rgb(1.f, 0.f, 1.f);                                     // shading.cpp:33
     return rgb(fminf(1.5f, E.r), fminf(1.5f, E.g), fminf(1.5f, E.b));        // shading.cpp:133-135
 }
 

@@ -139,6 +139,28 @@ def test_wavefront_and_per_thread_kernels_agree(gpu, name, monkeypatch):
         assert out["0stats"][k] == out["1stats"][k], k
 
 
+@pytest.mark.parametrize("name", ["snorlax_small", "pokeballs_small", "penguin_small", "synthetic_a_tiny"])
+def test_flat_kernel_and_generic_loop_agree(gpu, name, monkeypatch):
+    """A scene in which no ray can spawn a child runs trace_flat (one closest hit + one shade, optionally with the CTA in
+    lockstep per light); forced back onto the generic stack loop (RT_FORCE_FLAT=0) or in / out of lockstep
+    (RT_FORCE_LOCKSTEP), frame, ids and ray counts must not change by a bit."""
+    out = []
+    for env in ({"RT_FORCE_FLAT": "0"}, {"RT_FORCE_LOCKSTEP": "0"}, {"RT_FORCE_LOCKSTEP": "1"}):
+        for k in ("RT_FORCE_FLAT", "RT_FORCE_LOCKSTEP"):
+            monkeypatch.delenv(k, raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        sc = gpu.load_scene_from_json(scene_path(name))
+        got, tr = render_gpu(gpu, sc, "standard")
+        out.append((got, dict(tr.last_stats)))
+        sc.close()
+    for got, st in out[1:]:
+        for k in ("rgb8", "fb", "ids"):
+            assert np.array_equal(out[0][0][k], got[k]), k
+        for k in ("primary_rays", "shadow_rays", "secondary_rays", "prim_tests"):
+            assert out[0][1][k] == st[k], k
+
+
 def test_every_scene_data_path_agrees(gpu, monkeypatch):
     """RT_FORCE_GLOBAL: the scene read through the global read-only path instead of the staged shared-memory image."""
     ref = None
