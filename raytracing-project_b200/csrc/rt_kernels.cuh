@@ -114,13 +114,15 @@ template <bool C, bool K, bool F>
 __global__ void __launch_bounds__(kRenderThreads, RT_MIN_BLOCKS) render_standard_kernel(RenderParams prm) {
     // raw generator words: [0, kN) the tile's checkpoint, then the 8 blocks it yields (tempered on use)
     __shared__ __align__(16) uint32_t raw[mt::kN + mt::kOutputsPerTile];
-    __shared__ int s_tile;
+    __shared__ int s_tile, s_next;
     const int tid = threadIdx.x;
+    constexpr int kWarpGroups = (mt::kSamplesPerTile + 31) / 32;           // 39 groups of 4 pixels per tile
+    constexpr int kWarps = kRenderThreads / 32;
     const int nx = c_hdr.nx, ny = c_hdr.ny;
     Counters cnt = {0, 0, 0, 0};
     stage_scene<C>();
     for (;;) {
-        if (tid == 0) s_tile = (int)atomicAdd(prm.tile_counter, 1u);
+        if (tid == 0) { s_tile = (int)atomicAdd(prm.tile_counter, 1u); s_next = 0; }
         __syncthreads();
         const int local = s_tile;
         if (local >= prm.n_local_tiles) break;
@@ -133,11 +135,24 @@ __global__ void __launch_bounds__(kRenderThreads, RT_MIN_BLOCKS) render_standard
             for (int k = tid; k < mt::kN; k += kRenderThreads) raw[(b + 1) * mt::kN + k] = mt::next_word(raw + b * mt::kN, k);
             __syncthreads();
         }
-        // --- one sample per thread; 8 consecutive lanes share a pixel ---
+        // --- one sample per thread; 8 consecutive lanes share a pixel.  A warp takes the tile's 39 groups of 32 samples
+        // from a shared counter, so a warp that drew expensive samples traces fewer groups and the barrier at the end of
+        // the tile waits for one group at most.  In lockstep the groups are dealt statically (every warp must run the same
+        // number of rounds: trace_flat has barriers inside). ---
         const long long pix0 = tile * mt::kPixelsPerTile;
 #pragma unroll 1
-        for (int pass = 0; pass < (mt::kSamplesPerTile + kRenderThreads - 1) / kRenderThreads; ++pass) {
-            const int j = pass * kRenderThreads + tid;
+        for (int round = 0;; ++round) {
+            int grp;
+            if (prm.lockstep) {
+                if (round * kWarps >= kWarpGroups) break;
+                grp = round * kWarps + (tid >> 5);
+            } else {
+                grp = 0;
+                if ((tid & 31) == 0) grp = atomicAdd(&s_next, 1);
+                grp = __shfl_sync(0xffffffffu, grp, 0);
+                if (grp >= kWarpGroups) break;
+            }
+            const int j = grp * 32 + (tid & 31);
             const long long p = pix0 + (j >> 3);
             const bool active = j < mt::kSamplesPerTile && p < prm.n_pixels;
             RGBf c = rgb(0.f, 0.f, 0.f);
