@@ -90,7 +90,7 @@ ABI_SYMBOLS = [
     "rt_init", "rt_shutdown", "rt_last_error", "rt_version",
     "rt_compile_json_text", "rt_compile_json_file", "rt_compiled_desc", "rt_compiled_free",
     "rt_scene_upload", "rt_scene_free", "rt_scene_size",
-    "rt_render", "rt_render_device", "rt_trace_rays", "rt_debug_jitter", "rt_debug_mt_block_host", "rt_debug_device_layout",
+    "rt_render", "rt_render_device", "rt_trace_rays", "rt_debug_jitter", "rt_debug_mt_block_host", "rt_debug_device_layout", "rt_debug_mask_table",
     "rt_measure_fp32_peak",
     "rt_write_png_rgb8",
     "rt_peer_frame_create", "rt_peer_frame_open", "rt_peer_frame_close",
@@ -187,6 +187,14 @@ class Scene:
         _check(lib().rt_debug_device_layout(C.byref(self.desc), order.ctypes.data_as(C.c_void_p), C.byref(nr),
                                             runs.ctypes.data_as(C.c_void_p), C.byref(nc), clusters.ctypes.data_as(C.c_void_p)))
         return order[:n], runs[: nr.value], clusters[: nc.value]
+
+    def mask_table(self):
+        """(masks[n,4], scale): the table of the device's conservative candidate scan (host-only; see rt_debug_mask_table)."""
+        n, scale = C.c_int(), C.c_float()
+        _check(lib().rt_debug_mask_table(C.byref(self.desc), C.byref(n), None, C.byref(scale)))
+        masks = np.zeros((max(n.value, 1), 4), np.float32)
+        _check(lib().rt_debug_mask_table(C.byref(self.desc), C.byref(n), masks.ctypes.data_as(C.c_void_p), C.byref(scale)))
+        return masks[: n.value], float(scale.value)
 
     def device_handle(self):
         if not self._device:

@@ -57,12 +57,13 @@ struct rt_scene {
     bool lockstep{false};     // flat scene with generic objects (CSG programs, wrapped primitives): see trace_flat
     bool bounces{false};      // most materials reflect or refract and medium.recursion >= 2: deep, uneven ray trees
     size_t smem_bytes{0};
-    std::vector<float4> obj_geom, leaf_geom, pokeballs, affines, materials, lights, fallbacks, clusters;
+    std::vector<float4> obj_geom, leaf_geom, pokeballs, affines, materials, lights, fallbacks, clusters, masks;
+    float mask_scale{0.f};
     std::vector<int4> obj_meta, leaf_meta, runs;
     std::vector<int> obj_orig;
     std::vector<uint32_t> ops;
     float4 *d_obj_geom{nullptr}, *d_leaf_geom{nullptr}, *d_pokeballs{nullptr}, *d_affines{nullptr}, *d_materials{nullptr},
-           *d_lights{nullptr}, *d_fallbacks{nullptr}, *d_clusters{nullptr};
+           *d_lights{nullptr}, *d_fallbacks{nullptr}, *d_clusters{nullptr}, *d_masks{nullptr};
     int* d_obj_orig{nullptr};
     int4 *d_obj_meta{nullptr}, *d_leaf_meta{nullptr}, *d_runs{nullptr};
     uint32_t* d_ops{nullptr};
@@ -214,6 +215,19 @@ void build_host_arrays(const rt_scene_desc& d, rt_scene& s) {
         s.runs.push_back(make_int4(kind, i, j - i, ctab));
         i = j;
     }
+    // Mask table of sphere_mask: (c, |c|^2 - r^2) for every entry of obj_geom | leaf_geom | clusters (entries that are not
+    // sphere-like are never scanned through it), and the scale of its rounding margin, max(|c|^2 + r^2) over finite entries.
+    double scale = 0.0;
+    auto add = [&](const float4& g, bool scanned) {
+        const double cc = (double)g.x * g.x + (double)g.y * g.y + (double)g.z * g.z, rr = (double)g.w * g.w;
+        s.masks.push_back(make_float4(g.x, g.y, g.z, (float)(cc - rr)));
+        if (scanned && std::isfinite(cc + rr)) scale = std::max(scale, cc + rr);
+    };
+    auto sphere_like = [](const int4& m) { return (m.x & 0xff) != RT_PRIM_HALFSPACE && !((m.x >> 8) & RT_FLAG_AFFINE); };
+    for (size_t i = 0; i < s.obj_geom.size(); ++i) add(s.obj_geom[i], sphere_like(s.obj_meta[i]));
+    for (size_t i = 0; i < s.leaf_geom.size(); ++i) add(s.leaf_geom[i], sphere_like(s.leaf_meta[i]));
+    for (const float4& g : s.clusters) add(g, true);
+    s.mask_scale = (float)std::min(scale * (1.0 + 1e-6), 3.0e38);
 }
 
 }  // namespace
@@ -286,7 +300,7 @@ int rt_scene_upload(const rt_scene_desc* d, rt_scene** out) {
         (rc = upload(s->ops, &s->d_ops)) || (rc = upload(s->materials, &s->d_materials)) ||
         (rc = upload(s->lights, &s->d_lights)) || (rc = upload(s->fallbacks, &s->d_fallbacks)) ||
         (rc = upload(s->runs, &s->d_runs)) || (rc = upload(s->clusters, &s->d_clusters)) ||
-        (rc = upload(s->obj_orig, &s->d_obj_orig))) { rt_scene_free(s); return rc; }
+        (rc = upload(s->obj_orig, &s->d_obj_orig)) || (rc = upload(s->masks, &s->d_masks))) { rt_scene_free(s); return rc; }
     rtd::SceneHeader& h = s->hdr;
     for (int k = 0; k < 3; ++k) { h.eye[k] = d->eye[k]; h.P[k] = d->screen_p[k]; h.bg[k] = d->background[k]; }
     h.lx = d->lx; h.ly = d->ly; h.nx = d->width; h.ny = d->height;
@@ -296,12 +310,14 @@ int rt_scene_upload(const rt_scene_desc* d, rt_scene** out) {
     h.pokeballs = s->d_pokeballs; h.affines = s->d_affines; h.ops = s->d_ops; h.materials = s->d_materials;
     h.lights = s->d_lights; h.fallbacks = s->d_fallbacks; h.runs = s->d_runs; h.clusters = s->d_clusters; h.obj_orig = s->d_obj_orig;
     h.n_clusters = (int)s->clusters.size();
+    h.masks = s->d_masks; h.mask_scale = s->mask_scale;
     s->width = d->width; s->height = d->height;
     h.n_leaves = d->n_leaves; h.n_ops = d->n_ops;
     h.off_leaf_geom = d->n_objects; h.off_leaf_meta = h.off_leaf_geom + d->n_leaves; h.off_runs = h.off_leaf_meta + d->n_leaves;
     h.off_lights = h.off_runs + (int)s->runs.size();
     h.off_clusters = h.off_lights + 2 * d->n_lights;
-    h.off_ops_bytes = 16 * (h.off_clusters + h.n_clusters);
+    h.off_masks = h.off_clusters + h.n_clusters;
+    h.off_ops_bytes = 16 * (h.off_masks + (int)s->masks.size());
     h.smem_bytes = h.off_ops_bytes + 4 * d->n_ops;
     s->smem_bytes = (size_t)h.smem_bytes;
     s->fits_const = s->smem_bytes <= kSceneSmemBudget;
@@ -325,7 +341,7 @@ void rt_scene_free(rt_scene* s) {
     if (g_ctx.const_owner == s) g_ctx.const_owner = nullptr;
     cudaFree(s->d_obj_geom); cudaFree(s->d_obj_meta); cudaFree(s->d_leaf_geom); cudaFree(s->d_leaf_meta);
     cudaFree(s->d_pokeballs); cudaFree(s->d_affines); cudaFree(s->d_ops); cudaFree(s->d_materials);
-    cudaFree(s->d_lights); cudaFree(s->d_fallbacks); cudaFree(s->d_runs); cudaFree(s->d_clusters); cudaFree(s->d_obj_orig);
+    cudaFree(s->d_lights); cudaFree(s->d_fallbacks); cudaFree(s->d_runs); cudaFree(s->d_clusters); cudaFree(s->d_obj_orig); cudaFree(s->d_masks);
     delete s;
 }
 
@@ -341,6 +357,16 @@ int rt_debug_device_layout(const rt_scene_desc* d, int* order /*n_objects*/, int
     if (runs4) for (size_t i = 0; i < s.runs.size(); ++i) { runs4[4 * i] = s.runs[i].x; runs4[4 * i + 1] = s.runs[i].y; runs4[4 * i + 2] = s.runs[i].z; runs4[4 * i + 3] = s.runs[i].w; }
     if (n_clusters) *n_clusters = (int)s.clusters.size();
     if (clusters4) for (size_t i = 0; i < s.clusters.size(); ++i) { clusters4[4 * i] = s.clusters[i].x; clusters4[4 * i + 1] = s.clusters[i].y; clusters4[4 * i + 2] = s.clusters[i].z; clusters4[4 * i + 3] = s.clusters[i].w; }
+    return RT_OK;
+}
+
+int rt_debug_mask_table(const rt_scene_desc* d, int* n, float* masks4, float* scale) {
+    if (!d) return fail(RT_ERR_ARG, "rt_debug_mask_table: null scene");
+    rt_scene s;
+    build_host_arrays(*d, s);
+    if (n) *n = (int)s.masks.size();
+    if (scale) *scale = s.mask_scale;
+    if (masks4) for (size_t i = 0; i < s.masks.size(); ++i) { masks4[4 * i] = s.masks[i].x; masks4[4 * i + 1] = s.masks[i].y; masks4[4 * i + 2] = s.masks[i].z; masks4[4 * i + 3] = s.masks[i].w; }
     return RT_OK;
 }
 

@@ -24,7 +24,8 @@ struct SceneHeader {
     float bg[3]; float medium_index;
     int recursion, n_objects, n_lights, n_runs, n_leaves, n_ops, n_clusters;
     // shared-memory image (units of 16 B from the start of dynamic shared memory; ops in bytes)
-    int off_leaf_geom, off_leaf_meta, off_runs, off_lights, off_clusters, off_ops_bytes, smem_bytes;
+    int off_leaf_geom, off_leaf_meta, off_runs, off_lights, off_clusters, off_masks, off_ops_bytes, smem_bytes;
+    float mask_scale;           // max |c|^2 + r^2 over the finite entries of `masks` (rounding margin of sphere_mask)
     const float4* obj_geom; const int4* obj_meta;
     const float4* leaf_geom; const int4* leaf_meta;
     const float4* pokeballs;    // 3 float4 each
@@ -36,9 +37,16 @@ struct SceneHeader {
     const int4* runs;           // kind, first, count, 1 + first cluster (0: run is not clustered)
     const float4* clusters;     // bounding sphere of every 16 consecutive primitives of a clustered run
     const int* obj_orig;        // JSON index of device object i (clustered runs are reordered spatially)
+    const float4* masks;        // (c.xyz, |c|^2 - r^2) of every entry of obj_geom, leaf_geom, clusters (in that order)
 };
 
 enum { RUN_SPHERE = 0, RUN_HALFSPACE = 1, RUN_POKEBALL = 2, RUN_GENERIC = 3 };
+
+// A/B build switch: 1 = the candidate scan evaluates the exact discriminant on the geometry arrays (13 FMA-pipe
+// instructions per primitive) instead of the conservative expanded form on the mask table (7).
+#ifndef RT_MASK_EXACT
+#define RT_MASK_EXACT 0
+#endif
 
 __constant__ SceneHeader c_hdr;
 extern __shared__ __align__(16) unsigned char s_scene[];
@@ -61,10 +69,17 @@ template <bool C> struct SV {
     static __device__ __forceinline__ float4 fallback(int i)  { return __ldg(c_hdr.fallbacks + i); }
     static __device__ __forceinline__ float4 cluster(int i)   { return C ? reinterpret_cast<const float4*>(s_scene)[c_hdr.off_clusters + i] : __ldg(c_hdr.clusters + i); }
     static __device__ __forceinline__ int    obj_orig(int i)  { return __ldg(c_hdr.obj_orig + i); }
-    // base pointers for sphere_mask
+    // base pointers for sphere_mask (the mask table mirrors obj_geom | leaf_geom | clusters)
+    static __device__ __forceinline__ const float4* mask_ptr(int i)    { return C ? reinterpret_cast<const float4*>(s_scene) + c_hdr.off_masks + i : c_hdr.masks + i; }
+#if RT_MASK_EXACT
     static __device__ __forceinline__ const float4* obj_ptr(int i)     { return C ? reinterpret_cast<const float4*>(s_scene) + i : c_hdr.obj_geom + i; }
     static __device__ __forceinline__ const float4* leaf_ptr(int i)    { return C ? reinterpret_cast<const float4*>(s_scene) + c_hdr.off_leaf_geom + i : c_hdr.leaf_geom + i; }
     static __device__ __forceinline__ const float4* cluster_ptr(int i) { return C ? reinterpret_cast<const float4*>(s_scene) + c_hdr.off_clusters + i : c_hdr.clusters + i; }
+#else
+    static __device__ __forceinline__ const float4* obj_ptr(int i)     { return mask_ptr(i); }
+    static __device__ __forceinline__ const float4* leaf_ptr(int i)    { return mask_ptr(c_hdr.n_objects + i); }
+    static __device__ __forceinline__ const float4* cluster_ptr(int i) { return mask_ptr(c_hdr.n_objects + c_hdr.n_leaves + i); }
+#endif
 };
 // Copy the scanned arrays into shared memory (all threads of the CTA; ends with a barrier).
 template <bool C> __device__ __forceinline__ void stage_scene() {
@@ -79,6 +94,8 @@ template <bool C> __device__ __forceinline__ void stage_scene() {
     for (int i = t; i < c_hdr.n_runs; i += n) reinterpret_cast<int4*>(dst)[c_hdr.off_runs + i] = __ldg(c_hdr.runs + i);
     for (int i = t; i < 2 * c_hdr.n_lights; i += n) dst[c_hdr.off_lights + i] = __ldg(c_hdr.lights + i);
     for (int i = t; i < c_hdr.n_clusters; i += n) dst[c_hdr.off_clusters + i] = __ldg(c_hdr.clusters + i);
+    const int n_masks = c_hdr.n_objects + c_hdr.n_leaves + c_hdr.n_clusters;
+    for (int i = t; i < n_masks; i += n) dst[c_hdr.off_masks + i] = __ldg(c_hdr.masks + i);
     uint32_t* ops = reinterpret_cast<uint32_t*>(s_scene + c_hdr.off_ops_bytes);
     for (int i = t; i < c_hdr.n_ops; i += n) ops[i] = __ldg(c_hdr.ops + i);
     __syncthreads();
@@ -104,6 +121,9 @@ __device__ __forceinline__ V3 normalized(V3 a) {
 }
 
 constexpr float kInf = __builtin_huge_valf();
+}  // namespace rtd
+#include "rt_csg.cuh"
+namespace rtd {
 
 struct Hit {
     float t; V3 n; int mat; int code; bool front;
@@ -148,15 +168,28 @@ __device__ __forceinline__ bool plane_t(float4 g, V3 o, V3 d, float tmin, float 
     return true;
 }
 
-// Candidate mask of a run of sphere-like primitives: bit k set <=> the LINE of the ray is not missed by
-// primitive first+k (disc >= 0; NaN counts as a candidate, as in `if (disc < 0) return false`).  This is the
-// FMA-dense inner loop of every scan: one broadcast LDS.128 + 13 FMA-pipe instructions + 1 compare per
-// primitive, no data-dependent branch, four independent chains in flight.  The (rare) candidates are then
-// finished in order by the caller with exactly the arithmetic of sphere_t / leaf_interval, so the result is
-// bit-identical to testing the primitives one after the other.   cnt <= 32.
+// Candidate mask of a run of sphere-like primitives: bit k set if the LINE of the ray may touch primitive first+k.
+// The mask is CONSERVATIVE (a superset of the primitives whose exact discriminant, sphere_disc, is >= 0; NaN counts as a
+// candidate, as in `if (disc < 0) return false`); every caller finishes the candidates in order with exactly the
+// arithmetic of sphere_t / leaf_interval and re-checks the discriminant there, so the result is bit-identical to
+// testing the primitives one after the other.  That freedom buys the cheap expanded form of the reference's own
+// quadratic (geometry.cpp:15-22): with the per-primitive constants m = (c, |c|^2 - r^2) of the mask table
+//     hb = o.d - c.d,   s = (|c|^2 - r^2) - 2 o.c,   candidate <=> hb^2 - s >= |o|^2 - margin
+// = 7 FMA-pipe instructions + 1 compare per primitive after one broadcast LDS.128, no data-dependent branch, four
+// independent chains in flight.  The form cancels (rounding error ~ 2^-24 (|o|^2 + |c|^2), where sphere_disc's is ~ r^2),
+// hence the margin 2^-16 (|o|^2 + max(|c|^2 + r^2)): it covers the rounding of both forms (< 70 of the 256 ulp of that scale) and
+// | |d|^2 - 1 | <= 2^-19 of directions normalised with the 2-ulp MUFU reciprocal; tests/test_mask_margin.py measures
+// the slack.  cnt <= 32.
 // Out of line on purpose: the scans call it from up to ten places (object runs, cluster bounds, cluster members,
 // generic-run bounds, CSG sphere runs; closest-hit and any-hit each); one copy keeps the kernel's hot code inside the
 // instruction cache (synthetic-A 2K 42.1 -> 30.4 ms, snorlax 4K 17.5 -> 16.8 ms).
+constexpr float kMaskMargin = 1.0f / 65536.0f;
+__device__ __forceinline__ bool mask_miss(float4 m, V3 m2o, V3 d, float od, float bound) {
+    const float hb = fmaf(-m.x, d.x, fmaf(-m.y, d.y, fmaf(-m.z, d.z, od)));
+    const float s = fmaf(m.x, m2o.x, fmaf(m.y, m2o.y, fmaf(m.z, m2o.z, m.w)));
+    return fmaf(hb, hb, -s) < bound;
+}
+#if RT_MASK_EXACT
 template <bool C> __device__ __noinline__ uint32_t sphere_mask(const float4* base, int cnt, V3 o, V3 d) {
     uint32_t mask = 0;
     int k = 0;
@@ -177,6 +210,30 @@ template <bool C> __device__ __noinline__ uint32_t sphere_mask(const float4* bas
     }
     return mask;
 }
+#else
+template <bool C> __device__ __noinline__ uint32_t sphere_mask(const float4* base, int cnt, V3 o, V3 d) {
+    const float oo = dot(o, o), od = dot(o, d);
+    const float bound = fmaf(-kMaskMargin, oo + c_hdr.mask_scale, oo) - 1e-30f;
+    const V3 m2o = mk(-2.f * o.x, -2.f * o.y, -2.f * o.z);
+    uint32_t mask = 0;
+    int k = 0;
+    for (; k + 4 <= cnt; k += 4) {
+        uint32_t nib = 0;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const float4 m = C ? base[k + u] : __ldg(base + k + u);
+            nib |= mask_miss(m, m2o, d, od, bound) ? 0u : (1u << u);
+        }
+        mask |= nib << k;
+    }
+#pragma unroll 1
+    for (; k < cnt; ++k) {
+        const float4 m = C ? base[k] : __ldg(base + k);
+        mask |= mask_miss(m, m2o, d, od, bound) ? 0u : (1u << k);
+    }
+    return mask;
+}
+#endif
 
 // pick_region_material (geometry.cpp:163-180) on the unit offset u; returns 0..4 = top,bottom,belt,ring,button
 template <bool C> __device__ __forceinline__ int pokeball_region(int pb, V3 u) {
@@ -233,14 +290,6 @@ template <bool C> __device__ __forceinline__ V3 sphere_outward(float4 g, int4 m,
     return out;
 }
 
-// ---- CSG programs (csg.cpp:61-163) ------------------------------------------------------------------
-// An interval end is (t, code): code = leaf | region<<20 | front<<23 | nmode<<24 | fallback<<26,
-// nmode 0 = geometric normal of the leaf at t, 1 = zero normal (csg.cpp:119), 2 = fallbacks[fallback].
-// Normals are evaluated lazily, only for the end that becomes the visible hit.
-struct Ivl { float t0, t1; uint32_t c0, c1; bool ok; };
-constexpr uint32_t kFrontBit = 1u << 23;
-constexpr uint32_t kNModeMask = 3u << 24;
-
 template <bool C> __device__ Ivl leaf_interval(int li, V3 o, V3 d, unsigned& tests) {
     Ivl r; r.ok = false; r.t0 = 0.f; r.t1 = 0.f; r.c0 = r.c1 = (uint32_t)li;
     float4 g = SV<C>::leaf_geom(li);
@@ -294,130 +343,11 @@ template <bool C> __device__ Ivl leaf_interval(int li, V3 o, V3 d, unsigned& tes
     return r;
 }
 
-__device__ __forceinline__ bool csg_in(int op, bool a, bool b) {
-    return op == RT_CSG_UNION ? (a || b) : op == RT_CSG_INTERSECTION ? (a && b) : (a && !b);
-}
-// event_less (csg.cpp:83-88); k = type | who<<1 (type 0 Enter, 1 Exit; who 0 A, 1 B)
-__device__ __forceinline__ bool ev_less(float ta, int ka, float tb, int kb) {
-    if (fabsf(ta - tb) > 1e-6f) return ta < tb;
-    if ((ka & 1) != (kb & 1)) return (ka & 1) == 0;
-    return (ka >> 1) < (kb >> 1);
-}
-
-// The synthetic entry CSG::interval records when the combined solid already contains the ray origin
-// (csg.cpp:92-96,114-122): t = 0, zero normal, front_face, material of the child's entry hit.
-__device__ __forceinline__ void origin_rewrite(Ivl& v) {
-    if (v.t0 < 1e-6f && v.t1 > 1e-6f) {
-        v.t0 = 0.f;
-        v.c0 = (v.c0 & ~(kNModeMask | (63u << 26))) | kFrontBit | (1u << 24);
-    }
-}
-// CSG::interval (csg.cpp:61-163) on two child intervals.
-__device__ Ivl csg_combine(int op, const Ivl& A, const Ivl& B) {
-    Ivl R; R.ok = false; R.t0 = 0.f; R.t1 = kInf; R.c0 = R.c1 = 0;
-    if (!A.ok && !B.ok) return R;
-    if (A.ok != B.ok) {
-        // One child missed.  With a finite, ordered interval X = [t0,t1] of the other child the sweep below
-        // reduces to: Intersection -> empty; Difference with only B -> empty; otherwise X itself, except that
-        // an X containing the ray origin gets the reference's synthetic entry at t=0 (csg.cpp:114-122).
-        const Ivl& X = A.ok ? A : B;
-        if (isfinite(X.t0) && isfinite(X.t1) && X.t0 <= X.t1) {
-            if (op == RT_CSG_INTERSECTION || (op == RT_CSG_DIFFERENCE && !A.ok)) return R;
-            R = X;
-            origin_rewrite(R);
-            return R;
-        }
-    }
-    float et[4]; int ek[4]; int n = 0;
-    // finite ends only (csg.cpp:76-81), initial order A-enter, A-exit, B-enter, B-exit
-    {
-        const float ts[4] = {A.t0, A.t1, B.t0, B.t1};
-        const bool ok[4] = {A.ok, A.ok, B.ok, B.ok};
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            bool use = ok[i] && isfinite(ts[i]);
-            // compact without dynamic indexing
-#pragma unroll
-            for (int k = 0; k < 4; ++k) if (use && k == n) { et[k] = ts[i]; ek[k] = i; }
-            n += use ? 1 : 0;
-        }
-    }
-    // libstdc++ insertion sort (std::sort on <= 16 elements), literal: comparator is not a strict weak order
-#pragma unroll
-    for (int i = 1; i < 4; ++i) {
-        if (i < n) {
-            float vt = et[i]; int vk = ek[i];
-            if (ev_less(vt, vk, et[0], ek[0])) {
-#pragma unroll
-                for (int k = i; k > 0; --k) { et[k] = et[k - 1]; ek[k] = ek[k - 1]; }
-                et[0] = vt; ek[0] = vk;
-            } else {
-                bool moving = true;
-#pragma unroll
-                for (int k = i; k > 0; --k) {
-                    if (moving && ev_less(vt, vk, et[k - 1], ek[k - 1])) { et[k] = et[k - 1]; ek[k] = ek[k - 1]; }
-                    else if (moving) { et[k] = vt; ek[k] = vk; moving = false; }
-                }
-                // (the unguarded loop always stops at k >= 1 because !less(val, first))
-            }
-        }
-    }
-    bool inA = A.ok && (A.t0 < 1e-6f) && (A.t1 > 1e-6f);       // csg.cpp:92-96
-    bool inB = B.ok && (B.t0 < 1e-6f) && (B.t1 > 1e-6f);
-    bool inR = csg_in(op, inA, inB);
-    bool haveEnter = false, done = false;
-    float tEnt = 0.f, tExt = kInf; uint32_t cEnt = 0, cExt = 0;
-    if (inR) {                                                 // csg.cpp:114-122: entry at t=0, zero normal, front
-        haveEnter = true;
-        uint32_t src = inA ? A.c0 : B.c0;
-        cEnt = (src & ~(kNModeMask | (63u << 26))) | kFrontBit | (1u << 24);
-    }
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {                              // csg.cpp:125-156
-        if (i < n && !done) {
-            const int k = ek[i];
-            const bool before = inR;
-            const bool enter = (k & 1) == 0;
-            if ((k >> 1) == 0) inA = enter; else inB = enter;
-            const bool after = csg_in(op, inA, inB);
-            const uint32_t code = k == 0 ? A.c0 : k == 1 ? A.c1 : k == 2 ? B.c0 : B.c1;
-            // A \ B: a boundary contributed by B has its normal negated and re-oriented (csg.cpp:140-142,148-150):
-            // the oriented normal is unchanged, front_face becomes false.
-            if (!before && after) {
-                haveEnter = true; tEnt = et[i];
-                cEnt = (op == RT_CSG_DIFFERENCE && k == 3) ? (code & ~kFrontBit) : code;
-            } else if (before && !after) {
-                tExt = et[i];
-                cExt = (op == RT_CSG_DIFFERENCE && k == 2) ? (code & ~kFrontBit) : code;
-                done = true;
-            }
-            inR = after;
-        }
-    }
-    if (!haveEnter || !isfinite(tExt)) return R;              // csg.cpp:158
-    R.ok = true; R.t0 = tEnt; R.t1 = tExt; R.c0 = cEnt; R.c1 = cExt;
-    return R;
-}
-
-// RT_OP_XFIX: what a transform node does to its child's interval besides moving geometry
-// (transform.cpp:57-86, 140-172, 225-255): ends re-projected from their hit point (non-finite -> 0),
-// zero normals replaced by normalized()'s fallback under Scaling/Rotation, front_face re-derived.
-__device__ __forceinline__ uint32_t xfix_code(uint32_t c, uint32_t arg) {
-    uint32_t nmode = (c >> 24) & 3u;
-    if (nmode == 1u && arg != 0xFFFFFu) { c = (c & ~(kNModeMask | (63u << 26))) | (2u << 24) | (arg << 26); nmode = 2u; }
-    return nmode == 1u ? (c & ~kFrontBit) : (c | kFrontBit);
-}
-__device__ __forceinline__ void xfix(Ivl& v, uint32_t arg) {
-    if (!v.ok) return;
-    if (!isfinite(v.t0)) v.t0 = 0.f;
-    if (!isfinite(v.t1)) v.t1 = 0.f;
-    v.c0 = xfix_code(v.c0, arg);
-    v.c1 = xfix_code(v.c1, arg);
-}
-
 // Out of line on purpose: inlined into both scans it cost 800 B of spills at 128 registers; as a call the kernel fits 64
 // registers (4 CTAs = 32 warps per SM) with 1/4 of the spills (snorlax 4K 20.5 -> 17.1 ms, synthetic-B 547 -> 486 ms).
-template <bool C> __device__ __noinline__ Ivl run_program(int first, int count, V3 o, V3 d, unsigned& tests) {
+struct ProgResult { Ivl v; unsigned tests; };       // tests: primitives examined (returned by value: a reference would pin the caller's counter to memory)
+template <bool C> __device__ __noinline__ ProgResult run_program(int first, int count, V3 o, V3 d) {
+    unsigned tests = 0;
     Ivl acc; acc.ok = false; acc.t0 = acc.t1 = 0.f; acc.c0 = acc.c1 = 0;
     Ivl stack[RT_MAX_CSG_STACK]; int sp = 0;
     for (int i = 0; i < count; ++i) {
@@ -438,6 +368,13 @@ template <bool C> __device__ __noinline__ Ivl run_program(int first, int count, 
                     int pos = 0;
                     for (;;) {
                         const int k = mask ? (__ffs(mask) - 1) : cnt;          // next candidate, or the end of the chunk
+                        float4 g = make_float4(0.f, 0.f, 0.f, 0.f); float hb = 0.f, disc = 0.f;
+                        if (k < cnt) {
+                            mask &= mask - 1;
+                            g = SV<C>::leaf_geom(base + k);
+                            disc = sphere_disc(g, o, d, hb);
+                            if (disc < 0.f) continue;                          // the mask is conservative: k is a miss like pos..k-1
+                        }
                         // ---- spheres pos..k-1 are missed: the one-child case of csg_combine, applied in order ----
                         if (k > pos && acc.ok) {
                             if (csg == RT_CSG_INTERSECTION) acc.ok = false;
@@ -451,10 +388,7 @@ template <bool C> __device__ __noinline__ Ivl run_program(int first, int count, 
                             }
                         }
                         if (k >= cnt) break;
-                        mask &= mask - 1; pos = k + 1;
-                        const float4 g = SV<C>::leaf_geom(base + k);
-                        float hb;
-                        const float disc = sphere_disc(g, o, d, hb);
+                        pos = k + 1;
                         const float sq = sqrtf(disc), ir = 1.f / g.w;
                         const bool xformed = (SV<C>::leaf_meta(base + k).x >> 8) & RT_FLAG_XFORMED;
                         Ivl b; b.ok = true; b.t0 = -hb - sq; b.t1 = -hb + sq;
@@ -467,7 +401,8 @@ template <bool C> __device__ __noinline__ Ivl run_program(int first, int count, 
             } break;
         }
     }
-    return acc;
+    ProgResult r; r.v = acc; r.tests = tests;
+    return r;
 }
 
 }  // namespace rtd

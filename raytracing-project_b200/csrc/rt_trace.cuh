@@ -31,7 +31,8 @@ __device__ bool generic_hit(int i, V3 o, V3 d, float tmin, float tmax, float& t_
             const float sq = sqrtf(disc);
             if (-hb + sq < 0.f || -hb - sq > tmax) return false;
         }
-        Ivl v = run_program<C>(m.z, m.w, o, d, tests);
+        const ProgResult pr = run_program<C>(m.z, m.w, o, d);
+        const Ivl v = pr.v; tests += pr.tests;
         if (!v.ok) return false;
         t = fmaxf(v.t0, lo);                                                 // csg.cpp:175-176
         if (!(t < v.t1 && t < hi)) return false;
