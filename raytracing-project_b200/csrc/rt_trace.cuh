@@ -57,7 +57,102 @@ __device__ bool generic_hit(int i, V3 o, V3 d, float tmin, float tmax, float& t_
     return true;
 }
 
-// ---- Scene::intersect (scene.cpp:10-24) ------------------------------------------------------------------
+// ---- Scene::intersect (scene.cpp:10-24) and Scene::occluded (scene.cpp:33-42): ONE scan -------------------------------
+// Both queries walk the object list in JSON order; `any` (Scene::occluded) stops at the first accepted hit, otherwise the
+// window's far end shrinks to the best hit so far (tmax == best_t until the first hit, so the two are the same loop).
+// One out-of-line copy serves the primary / secondary rays and the shadow rays: all warps of an SM spend most of their
+// time in this one function, so its code stays resident in the instruction cache (two inlined copies, one in trace and
+// one in shade, did not: `no_instruction` was the top stall of the generic kernel).  The test count is returned by
+// value (a reference would pin the caller's counter to local memory).
+struct ScanResult { int best; float t; uint32_t code; float tent; unsigned tests; };
+
+#ifndef RT_SCAN_INLINE
+#define RT_SCAN_INLINE 0
+#endif
+#if RT_SCAN_INLINE
+#define RT_SCAN_FN __device__ __forceinline__
+#else
+#define RT_SCAN_FN __device__ __noinline__
+#endif
+
+template <bool C, bool K>
+RT_SCAN_FN ScanResult scan_scene(V3 o, V3 d, float tmin, float tmax, bool any) {
+    int best = -1; float best_t = tmax; uint32_t best_code = 0; float best_tent = 0.f; unsigned tests = 0;
+    const int n_runs = c_hdr.n_runs;
+    for (int r = 0; r < n_runs; ++r) {
+        const int4 run = SV<C>::run(r);
+        const int first = run.y, end = run.y + run.z;
+        if (K && (run.x == RUN_SPHERE || run.x == RUN_POKEBALL) && run.w > 0) {
+            // Clustered run (spatially reordered, 16 primitives per cluster): candidate mask over the cluster bounds,
+            // then over the members of the clusters whose bound overlaps the window.  A sphere's candidate root does
+            // not depend on the order of the scan; exact ties go to the later JSON index as in scene.cpp:15-21.
+            const int ctab = run.w - 1, ncl = (run.z + 15) >> 4;
+            tests += ncl;
+            for (int cb = 0; cb < ncl; cb += 32) {
+                uint32_t cmask = sphere_mask<C>(SV<C>::cluster_ptr(ctab + cb), min(32, ncl - cb), o, d);
+                while (cmask) {
+                    const int c = cb + __ffs(cmask) - 1; cmask &= cmask - 1;
+                    float hb;
+                    const float disc = sphere_disc(SV<C>::cluster(ctab + c), o, d, hb);
+                    const float sq = sqrtf(disc);
+                    if (-hb + sq < 0.f || -hb - sq > best_t) continue;
+                    const int m0 = first + 16 * c, n = min(16, end - m0);
+                    tests += n;
+                    uint32_t mask = sphere_mask<C>(SV<C>::obj_ptr(m0), n, o, d);
+                    while (mask) {
+                        const int i = m0 + __ffs(mask) - 1; mask &= mask - 1;
+                        float t;
+                        if (!sphere_t(SV<C>::obj_geom(i), o, d, tmin, best_t, t)) continue;
+                        if (t == best_t && best >= 0 && SV<C>::obj_orig(i) < SV<C>::obj_orig(best)) continue;
+                        best = i; best_t = t;
+                        if (any) goto done;
+                    }
+                }
+            }
+        } else if (run.x == RUN_SPHERE || run.x == RUN_POKEBALL) {
+            for (int c0 = first; c0 < end; c0 += 32) {                       // candidates first, finished in JSON order
+                const int n = min(32, end - c0);
+                tests += n;
+                uint32_t mask = sphere_mask<C>(SV<C>::obj_ptr(c0), n, o, d);
+                while (mask) {
+                    const int i = c0 + __ffs(mask) - 1; mask &= mask - 1;
+                    float t;
+                    if (sphere_t(SV<C>::obj_geom(i), o, d, tmin, best_t, t)) { best = i; best_t = t; if (any) goto done; }
+                }
+            }
+        } else if (run.x == RUN_HALFSPACE) {
+            for (int i = first; i < end; ++i) {
+                float t; ++tests;
+                if (plane_t(SV<C>::obj_geom(i), o, d, tmin, best_t, t)) { best = i; best_t = t; if (any) goto done; }
+            }
+        } else {
+            // generic objects (CSG programs, wrapped / affine primitives); a long run has one world bound per object,
+            // scanned with the candidate mask first
+            const bool bounded = K && run.w > 0;
+            const int ctab = run.w - 1;
+            if (bounded) tests += run.z;
+            for (int c0 = first; c0 < end; c0 += 32) {
+                const int n = min(32, end - c0);
+                uint32_t mask = bounded ? sphere_mask<C>(SV<C>::cluster_ptr(ctab + c0 - first), n, o, d) : (n == 32 ? 0xffffffffu : (1u << n) - 1u);
+                while (mask) {
+                    const int i = c0 + __ffs(mask) - 1; mask &= mask - 1;
+                    float t, tent; uint32_t code;
+                    if (generic_hit<C>(i, o, d, tmin, best_t, t, code, tent, tests)) {
+                        best = i; best_t = t; best_code = code; best_tent = tent;
+                        if (any) goto done;
+                    }
+                }
+            }
+        }
+    }
+done:
+    ScanResult res; res.best = best; res.t = best_t; res.code = best_code; res.tent = best_tent; res.tests = tests;
+    return res;
+}
+
+// Scenes without clustered runs / per-object bounds (K = false: a few dozen primitives) keep the two scans inlined and
+// specialised: their hot code fits the instruction cache anyway and the call costs more than it saves (snorlax 4K 12.6 ->
+// 14.3 ms, pokeballs 0.54 -> 0.69 ms with the out-of-line scan; the 1 100-primitive scene 29.0 -> 23.7 ms).
 // One run of the object list against the best hit so far.
 template <bool C, bool K>
 __device__ __forceinline__ void run_closest(const int4 run, V3 o, V3 d, float tmin, int& best, float& best_t, uint32_t& best_code,
@@ -127,50 +222,6 @@ __device__ __forceinline__ void run_closest(const int4 run, V3 o, V3 d, float tm
 }
 
 template <bool C, bool K>
-__device__ bool closest_hit(V3 o, V3 d, float tmin, float tmax, Hit& hit, Counters& cnt) {
-    int best = -1; float best_t = tmax; uint32_t best_code = 0; float best_tent = 0.f;
-    const int n_runs = c_hdr.n_runs;
-    for (int r = 0; r < n_runs; ++r) run_closest<C, K>(SV<C>::run(r), o, d, tmin, best, best_t, best_code, best_tent, cnt);
-    if (best < 0) return false;
-    // ---- finalise the winner: normal, front_face, material, id code ----
-    const int4 m = SV<C>::obj_meta(best);
-    const int kind = m.x & 0xff, flags = m.x >> 8;
-    hit.t = best_t;
-    hit.code = SV<C>::obj_orig(best) * 8;
-    V3 outward; bool front; int mat;
-    if (kind == RT_PRIM_PROGRAM) {
-        const uint32_t code = best_code;
-        const int li = code & 0xFFFFF, region = (code >> 20) & 7, nmode = (code >> 24) & 3;
-        const int4 lm = SV<C>::leaf_meta(li);
-        mat = lm.y + region;
-        front = (code & kFrontBit) != 0;
-        V3 n;
-        if (nmode == 1) n = mk(0.f, 0.f, 0.f);                               // csg.cpp:119
-        else {
-            if (nmode == 2) { float4 f = SV<C>::fallback(code >> 26); outward = mk(f.x, f.y, f.z); }
-            else if ((lm.x & 0xff) == RT_PRIM_HALFSPACE) { float4 g = SV<C>::leaf_geom(li); outward = mk(g.x, g.y, g.z); }
-            else { int rg; outward = sphere_outward<C>(SV<C>::leaf_geom(li), lm, o, d, best_tent, rg); }
-            n = dot(d, outward) < 0.f ? outward : neg(outward);              // geometry.h:42-45
-        }
-        if (flags & RT_FLAG_WRAPPED) front = dot(d, n) < 0.f;               // transform.cpp:41
-        hit.n = n; hit.mat = mat; hit.front = front;
-        return true;
-    }
-    const float4 g = SV<C>::obj_geom(best);
-    int region = 0;
-    if (kind == RT_PRIM_HALFSPACE) outward = mk(g.x, g.y, g.z);
-    else outward = sphere_outward<C>(g, m, o, d, best_t, region);
-    front = dot(d, outward) < 0.f;
-    V3 n = front ? outward : neg(outward);
-    if (flags & RT_FLAG_XFORMED) front = dot(d, n) < 0.f;                   // transform.cpp:41
-    mat = m.y;
-    if (kind == RT_PRIM_POKEBALL) { mat += region; if (!(flags & RT_FLAG_XFORMED)) hit.code += region + 1; }   // code: only a bare top-level pokeball reports its region
-    hit.n = n; hit.mat = mat; hit.front = front;
-    return true;
-}
-
-// ---- Scene::occluded (scene.cpp:33-42) ---------------------------------------------------------------------
-template <bool C, bool K>
 __device__ __forceinline__ bool run_occludes(const int4 run, V3 o, V3 d, float tmin, float tmax, Counters& cnt) {
     {
         const int first = run.y, end = run.y + run.z;
@@ -233,7 +284,61 @@ __device__ __forceinline__ bool run_occludes(const int4 run, V3 o, V3 d, float t
 }
 
 template <bool C, bool K>
-__device__ bool occluded(V3 o, V3 d, float tmin, float tmax, Counters& cnt) {
+__device__ __forceinline__ bool closest_hit(V3 o, V3 d, float tmin, float tmax, Hit& hit, Counters& cnt) {
+    int best = -1; float best_t = tmax; uint32_t best_code = 0; float best_tent = 0.f;
+    if (K) {
+        const ScanResult sr = scan_scene<C, K>(o, d, tmin, tmax, false);
+        cnt.tests += sr.tests;
+        best = sr.best; best_t = sr.t; best_code = sr.code; best_tent = sr.tent;
+    } else {
+        const int n_runs = c_hdr.n_runs;
+        for (int r = 0; r < n_runs; ++r) run_closest<C, K>(SV<C>::run(r), o, d, tmin, best, best_t, best_code, best_tent, cnt);
+    }
+    if (best < 0) return false;
+    // ---- finalise the winner: normal, front_face, material, id code ----
+    const int4 m = SV<C>::obj_meta(best);
+    const int kind = m.x & 0xff, flags = m.x >> 8;
+    hit.t = best_t;
+    hit.code = SV<C>::obj_orig(best) * 8;
+    V3 outward; bool front; int mat;
+    if (kind == RT_PRIM_PROGRAM) {
+        const uint32_t code = best_code;
+        const int li = code & 0xFFFFF, region = (code >> 20) & 7, nmode = (code >> 24) & 3;
+        const int4 lm = SV<C>::leaf_meta(li);
+        mat = lm.y + region;
+        front = (code & kFrontBit) != 0;
+        V3 n;
+        if (nmode == 1) n = mk(0.f, 0.f, 0.f);                               // csg.cpp:119
+        else {
+            if (nmode == 2) { float4 f = SV<C>::fallback(code >> 26); outward = mk(f.x, f.y, f.z); }
+            else if ((lm.x & 0xff) == RT_PRIM_HALFSPACE) { float4 g = SV<C>::leaf_geom(li); outward = mk(g.x, g.y, g.z); }
+            else { int rg; outward = sphere_outward<C>(SV<C>::leaf_geom(li), lm, o, d, best_tent, rg); }
+            n = dot(d, outward) < 0.f ? outward : neg(outward);              // geometry.h:42-45
+        }
+        if (flags & RT_FLAG_WRAPPED) front = dot(d, n) < 0.f;               // transform.cpp:41
+        hit.n = n; hit.mat = mat; hit.front = front;
+        return true;
+    }
+    const float4 g = SV<C>::obj_geom(best);
+    int region = 0;
+    if (kind == RT_PRIM_HALFSPACE) outward = mk(g.x, g.y, g.z);
+    else outward = sphere_outward<C>(g, m, o, d, best_t, region);
+    front = dot(d, outward) < 0.f;
+    V3 n = front ? outward : neg(outward);
+    if (flags & RT_FLAG_XFORMED) front = dot(d, n) < 0.f;                   // transform.cpp:41
+    mat = m.y;
+    if (kind == RT_PRIM_POKEBALL) { mat += region; if (!(flags & RT_FLAG_XFORMED)) hit.code += region + 1; }   // code: only a bare top-level pokeball reports its region
+    hit.n = n; hit.mat = mat; hit.front = front;
+    return true;
+}
+
+template <bool C, bool K>
+__device__ __forceinline__ bool occluded(V3 o, V3 d, float tmin, float tmax, Counters& cnt) {
+    if (K) {
+        const ScanResult sr = scan_scene<C, K>(o, d, tmin, tmax, true);
+        cnt.tests += sr.tests;
+        return sr.best >= 0;
+    }
     const int n_runs = c_hdr.n_runs;
     for (int r = 0; r < n_runs; ++r)
         if (run_occludes<C, K>(SV<C>::run(r), o, d, tmin, tmax, cnt)) return true;
