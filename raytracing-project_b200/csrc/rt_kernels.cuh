@@ -217,6 +217,7 @@ __global__ void __launch_bounds__(kRenderThreads, RT_WAVE_BLOCKS) render_wavefro
     __shared__ __align__(16) uint32_t outw[mt::kOutputsPerTile];
     __shared__ unsigned short s_list[2][kWaveSamples];
     __shared__ int s_count[2];
+    __shared__ int s_cursor;
     __shared__ int s_tile[kWaveTiles];
     const int tid = threadIdx.x;
     const unsigned lane = tid & 31u;
@@ -231,7 +232,7 @@ __global__ void __launch_bounds__(kRenderThreads, RT_WAVE_BLOCKS) render_wavefro
         if (tid == 0) {
             const int first = (int)atomicAdd(prm.tile_counter, (unsigned)kWaveTiles);
             for (int t = 0; t < kWaveTiles; ++t) s_tile[t] = first + t;
-            s_count[0] = 0; s_count[1] = 0;
+            s_count[0] = 0; s_count[1] = 0; s_cursor = 0;
         }
         __syncthreads();
         if (s_tile[0] >= prm.n_local_tiles) break;
@@ -279,8 +280,14 @@ __global__ void __launch_bounds__(kRenderThreads, RT_WAVE_BLOCKS) render_wavefro
         for (;;) {                                                   // one ray of every unfinished sample per iteration
             const int n = s_count[q];
             if (n == 0) break;
-            for (int k0 = 0; k0 < n; k0 += kRenderThreads) {
-                const int k = k0 + tid;
+            // warps take 32 queue entries at a time from a shared cursor: a warp whose rays were cheap takes more, so the
+            // barrier at the end of the iteration waits for one batch of 32 at most
+            for (;;) {
+                int k = 0;
+                if (lane == 0) k = atomicAdd(&s_cursor, 32);
+                k = __shfl_sync(0xffffffffu, k, 0);
+                if (k >= n) break;
+                k += (int)lane;
                 bool more = false; int sid = 0;
                 if (k < n) {
                     sid = s_list[q][k];
@@ -322,7 +329,7 @@ __global__ void __launch_bounds__(kRenderThreads, RT_WAVE_BLOCKS) render_wavefro
                 }
             }
             __syncthreads();
-            if (tid == 0) s_count[q] = 0;
+            if (tid == 0) { s_count[q] = 0; s_cursor = 0; }
             q ^= 1;
             __syncthreads();
         }

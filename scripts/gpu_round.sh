@@ -17,7 +17,7 @@ python scripts/gpu_parity.py > $OUT/parity.log 2>&1
 python bench.py --steps 2 --warmup 3 --no-cpu > $OUT/plain_bench.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/launches_bench.csv \
     python bench.py --steps 2 --warmup 3 --no-cpu > $OUT/ncu_bench.log 2>&1
-for sc in snorlax_4k synthetic_a_2k synthetic_b_small; do
+for sc in snorlax_4k synthetic_a_2k synthetic_b_1k; do
 python scripts/profile_run.py scenes/$sc.json standard 2 > $OUT/plain_prof_$sc.log 2>&1 &&
 ncu --set full --clock-control none --import-source on -k "regex:render_(standard|wavefront)" -s 1 -c 1 -o $OUT/prof_$sc \
     python scripts/profile_run.py scenes/$sc.json standard 2 > $OUT/ncu_prof_$sc.log 2>&1
