@@ -313,7 +313,8 @@ int rt_scene_upload(const rt_scene_desc* d, rt_scene** out) {
     h.masks = s->d_masks; h.mask_scale = s->mask_scale;
     s->width = d->width; s->height = d->height;
     h.n_leaves = d->n_leaves; h.n_ops = d->n_ops;
-    h.off_leaf_geom = d->n_objects; h.off_leaf_meta = h.off_leaf_geom + d->n_leaves; h.off_runs = h.off_leaf_meta + d->n_leaves;
+    h.off_leaf_geom = s->clusters.empty() ? d->n_objects : 0;        // scenes with bounds read top-level geometry from global memory
+    h.off_leaf_meta = h.off_leaf_geom + d->n_leaves; h.off_runs = h.off_leaf_meta + d->n_leaves;
     h.off_lights = h.off_runs + (int)s->runs.size();
     h.off_clusters = h.off_lights + 2 * d->n_lights;
     h.off_masks = h.off_clusters + h.n_clusters;
@@ -470,7 +471,7 @@ int launch_frame(rt_scene* s, int mode, int rank, int world, uchar4* rgba8, floa
     const long long units = s->bounces ? (local + rtd::kWaveTiles - 1) / rtd::kWaveTiles : local;      // the wavefront kernel takes tiles in batches
     const long long grid = std::max<long long>(1, std::min<long long>(units, (long long)g_ctx.sms * std::max(per_sm, 1)));
     if (s->bounces) {
-        const size_t stride = 2 + 3 * (size_t)std::max(s->hdr.recursion, 1);
+        const size_t stride = (size_t)rtd::wave_stride(s->hdr.recursion);
         int rcw = grow(&g_ctx.d_wave, &g_ctx.wave_cap, (size_t)grid * rtd::kWaveSamples * stride * sizeof(float4)); if (rcw) return rcw;
         prm.wave_state = g_ctx.d_wave;
     }

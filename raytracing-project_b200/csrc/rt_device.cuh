@@ -58,6 +58,9 @@ extern __shared__ __align__(16) unsigned char s_scene[];
 // tables, affine maps, materials) is indexed per lane and always comes from global memory.
 template <bool C> struct SV {
     static __device__ __forceinline__ float4 obj_geom(int i)  { return C ? reinterpret_cast<const float4*>(s_scene)[i] : __ldg(c_hdr.obj_geom + i); }
+    // Scenes with bounds (K) do not stage the top-level geometry: the scan reads the mask table, geometry is only needed to
+    // finish the few candidates, and without it the 1 100-primitive scene keeps 4 CTAs per SM (43 -> 26 KB per CTA).
+    template <bool K> static __device__ __forceinline__ float4 obj_geom_k(int i) { return (C && !K) ? reinterpret_cast<const float4*>(s_scene)[i] : __ldg(c_hdr.obj_geom + i); }
     static __device__ __forceinline__ int4   obj_meta(int i)  { return __ldg(c_hdr.obj_meta + i); }
     static __device__ __forceinline__ float4 leaf_geom(int i) { return C ? reinterpret_cast<const float4*>(s_scene)[c_hdr.off_leaf_geom + i] : __ldg(c_hdr.leaf_geom + i); }
     static __device__ __forceinline__ int4   leaf_meta(int i) { return C ? reinterpret_cast<const int4*>(s_scene)[c_hdr.off_leaf_meta + i] : __ldg(c_hdr.leaf_meta + i); }
@@ -86,7 +89,7 @@ template <bool C> __device__ __forceinline__ void stage_scene() {
     if (!C) return;
     float4* dst = reinterpret_cast<float4*>(s_scene);
     const int t = threadIdx.x, n = blockDim.x;
-    for (int i = t; i < c_hdr.n_objects; i += n) dst[i] = __ldg(c_hdr.obj_geom + i);
+    for (int i = t; i < c_hdr.off_leaf_geom; i += n) dst[i] = __ldg(c_hdr.obj_geom + i);      // 0 entries when the scene has bounds
     for (int i = t; i < c_hdr.n_leaves; i += n) {
         dst[c_hdr.off_leaf_geom + i] = __ldg(c_hdr.leaf_geom + i);
         reinterpret_cast<int4*>(dst)[c_hdr.off_leaf_meta + i] = __ldg(c_hdr.leaf_meta + i);

@@ -209,6 +209,7 @@ __global__ void __launch_bounds__(kRenderThreads, RT_MIN_BLOCKS) render_standard
 #define RT_WAVE_TILES 1
 #endif
 constexpr int kWaveTiles = RT_WAVE_TILES;
+__host__ __device__ __forceinline__ int wave_stride(int recursion) { return (2 + 3 * (recursion > 1 ? recursion : 1) + 7) & ~7; }
 constexpr int kWaveSamples = kWaveTiles * mt::kSamplesPerTile;
 
 template <bool C, bool K>
@@ -223,7 +224,9 @@ __global__ void __launch_bounds__(kRenderThreads, RT_WAVE_BLOCKS) render_wavefro
     const unsigned lane = tid & 31u;
     const int nx = c_hdr.nx, ny = c_hdr.ny;
     const int limit = c_hdr.recursion;
-    const int stride = 2 + 3 * max(limit, 1);                        // float4 per sample
+    // float4 per sample: ray (2) + 3 per depth, padded to whole 128-byte lines so that the ray and the two shallowest levels
+    // of every sample share ONE line (with the unpadded 320-byte stride every other sample straddled two)
+    const int stride = wave_stride(limit);
     float4* my_state = prm.wave_state + (size_t)blockIdx.x * kWaveSamples * stride;
     Counters cnt = {0, 0, 0, 0};
     stage_scene<C>();
@@ -282,11 +285,20 @@ __global__ void __launch_bounds__(kRenderThreads, RT_WAVE_BLOCKS) render_wavefro
             if (n == 0) break;
             // warps take 32 queue entries at a time from a shared cursor: a warp whose rays were cheap takes more, so the
             // barrier at the end of the iteration waits for one batch of 32 at most
+            // (the NEXT batch is taken, and the first line of its samples' state prefetched, before the current one is traced:
+            // the state round-trips through L2 / HBM between iterations and its latency was the kernel's top stall)
+            int k_next = 0;
+            if (lane == 0) k_next = atomicAdd(&s_cursor, 32);
+            k_next = __shfl_sync(0xffffffffu, k_next, 0);
             for (;;) {
-                int k = 0;
-                if (lane == 0) k = atomicAdd(&s_cursor, 32);
-                k = __shfl_sync(0xffffffffu, k, 0);
+                int k = k_next;
                 if (k >= n) break;
+                if (lane == 0) k_next = atomicAdd(&s_cursor, 32);
+                k_next = __shfl_sync(0xffffffffu, k_next, 0);
+                if (k_next + (int)lane < n) {
+                    const float4* nx_state = my_state + (size_t)s_list[q][k_next + (int)lane] * stride;
+                    asm volatile("prefetch.global.L1 [%0];" :: "l"(nx_state));
+                }
                 k += (int)lane;
                 bool more = false; int sid = 0;
                 if (k < n) {

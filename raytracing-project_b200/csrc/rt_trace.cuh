@@ -10,7 +10,7 @@ namespace rtd {
 // windows are [tmin,tmax] (sphere/plane/pokeball, geometry.cpp:26-28,99), CSG uses t<tmax
 // (csg.cpp:176), transform-wrapped objects tmin<t<tmax (transform.cpp:38).  For programs the entry
 // code and raw entry time are returned for the deferred normal.
-template <bool C>
+template <bool C, bool K>
 __device__ bool generic_hit(int i, V3 o, V3 d, float tmin, float tmax, float& t_out, uint32_t& code_out, float& tent_out, unsigned& tests) {
     const int4 m = SV<C>::obj_meta(i);
     const int kind = m.x & 0xff, flags = m.x >> 8;
@@ -22,7 +22,7 @@ __device__ bool generic_hit(int i, V3 o, V3 d, float tmin, float tmax, float& t_
         // Conservative bounding sphere of the program's leaves (scene compiler; w < 0: none).  A ray whose line
         // misses it misses every leaf, so CSG::interval fails (csg.cpp:158); if all of it lies behind the
         // origin or beyond the window the first inside run cannot pass csg.cpp:175-176 / transform.cpp:38.
-        const float4 bs = SV<C>::obj_geom(i);
+        const float4 bs = SV<C>::template obj_geom_k<K>(i);
         if (bs.w >= 0.f) {
             ++tests;
             float hb;
@@ -39,7 +39,7 @@ __device__ bool generic_hit(int i, V3 o, V3 d, float tmin, float tmax, float& t_
         code_out = v.c0; tent_out = v.t0;
     } else {
         ++tests;
-        const float4 g = SV<C>::obj_geom(i);
+        const float4 g = SV<C>::template obj_geom_k<K>(i);
         if (kind == RT_PRIM_HALFSPACE) {
             if (!plane_t(g, o, d, lo, hi, t)) return false;
         } else if (flags & RT_FLAG_AFFINE) {
@@ -102,7 +102,7 @@ RT_SCAN_FN ScanResult scan_scene(V3 o, V3 d, float tmin, float tmax, bool any) {
                     while (mask) {
                         const int i = m0 + __ffs(mask) - 1; mask &= mask - 1;
                         float t;
-                        if (!sphere_t(SV<C>::obj_geom(i), o, d, tmin, best_t, t)) continue;
+                        if (!sphere_t(SV<C>::template obj_geom_k<K>(i), o, d, tmin, best_t, t)) continue;
                         if (t == best_t && best >= 0 && SV<C>::obj_orig(i) < SV<C>::obj_orig(best)) continue;
                         best = i; best_t = t;
                         if (any) goto done;
@@ -117,13 +117,13 @@ RT_SCAN_FN ScanResult scan_scene(V3 o, V3 d, float tmin, float tmax, bool any) {
                 while (mask) {
                     const int i = c0 + __ffs(mask) - 1; mask &= mask - 1;
                     float t;
-                    if (sphere_t(SV<C>::obj_geom(i), o, d, tmin, best_t, t)) { best = i; best_t = t; if (any) goto done; }
+                    if (sphere_t(SV<C>::template obj_geom_k<K>(i), o, d, tmin, best_t, t)) { best = i; best_t = t; if (any) goto done; }
                 }
             }
         } else if (run.x == RUN_HALFSPACE) {
             for (int i = first; i < end; ++i) {
                 float t; ++tests;
-                if (plane_t(SV<C>::obj_geom(i), o, d, tmin, best_t, t)) { best = i; best_t = t; if (any) goto done; }
+                if (plane_t(SV<C>::template obj_geom_k<K>(i), o, d, tmin, best_t, t)) { best = i; best_t = t; if (any) goto done; }
             }
         } else {
             // generic objects (CSG programs, wrapped / affine primitives); a long run has one world bound per object,
@@ -137,7 +137,7 @@ RT_SCAN_FN ScanResult scan_scene(V3 o, V3 d, float tmin, float tmax, bool any) {
                 while (mask) {
                     const int i = c0 + __ffs(mask) - 1; mask &= mask - 1;
                     float t, tent; uint32_t code;
-                    if (generic_hit<C>(i, o, d, tmin, best_t, t, code, tent, tests)) {
+                    if (generic_hit<C, K>(i, o, d, tmin, best_t, t, code, tent, tests)) {
                         best = i; best_t = t; best_code = code; best_tent = tent;
                         if (any) goto done;
                     }
@@ -179,7 +179,7 @@ __device__ __forceinline__ void run_closest(const int4 run, V3 o, V3 d, float tm
                     while (mask) {
                         const int i = m0 + __ffs(mask) - 1; mask &= mask - 1;
                         float t;
-                        if (!sphere_t(SV<C>::obj_geom(i), o, d, tmin, best_t, t)) continue;
+                        if (!sphere_t(SV<C>::template obj_geom_k<K>(i), o, d, tmin, best_t, t)) continue;
                         if (t == best_t && best >= 0 && SV<C>::obj_orig(i) < SV<C>::obj_orig(best)) continue;
                         best = i; best_t = t;
                     }
@@ -192,14 +192,14 @@ __device__ __forceinline__ void run_closest(const int4 run, V3 o, V3 d, float tm
                 while (mask) {
                     const int i = c0 + __ffs(mask) - 1; mask &= mask - 1;
                     float t;
-                    if (sphere_t(SV<C>::obj_geom(i), o, d, tmin, best_t, t)) { best = i; best_t = t; }
+                    if (sphere_t(SV<C>::template obj_geom_k<K>(i), o, d, tmin, best_t, t)) { best = i; best_t = t; }
                 }
             }
         } else if (run.x == RUN_HALFSPACE) {
             cnt.tests += run.z;
             for (int i = first; i < end; ++i) {
                 float t;
-                if (plane_t(SV<C>::obj_geom(i), o, d, tmin, best_t, t)) { best = i; best_t = t; }
+                if (plane_t(SV<C>::template obj_geom_k<K>(i), o, d, tmin, best_t, t)) { best = i; best_t = t; }
             }
         } else if (K && run.w > 0) {                   // generic run with per-object world bounds: candidates only
             const int ctab = run.w - 1;
@@ -209,13 +209,13 @@ __device__ __forceinline__ void run_closest(const int4 run, V3 o, V3 d, float tm
                 while (mask) {
                     const int i = c0 + __ffs(mask) - 1; mask &= mask - 1;
                     float t, tent; uint32_t code;
-                    if (generic_hit<C>(i, o, d, tmin, best_t, t, code, tent, cnt.tests)) { best = i; best_t = t; best_code = code; best_tent = tent; }
+                    if (generic_hit<C, K>(i, o, d, tmin, best_t, t, code, tent, cnt.tests)) { best = i; best_t = t; best_code = code; best_tent = tent; }
                 }
             }
         } else {
             for (int i = first; i < end; ++i) {
                 float t, tent; uint32_t code;
-                if (generic_hit<C>(i, o, d, tmin, best_t, t, code, tent, cnt.tests)) { best = i; best_t = t; best_code = code; best_tent = tent; }
+                if (generic_hit<C, K>(i, o, d, tmin, best_t, t, code, tent, cnt.tests)) { best = i; best_t = t; best_code = code; best_tent = tent; }
             }
         }
     }
@@ -242,7 +242,7 @@ __device__ __forceinline__ bool run_occludes(const int4 run, V3 o, V3 d, float t
                     while (mask) {
                         const int i = m0 + __ffs(mask) - 1; mask &= mask - 1;
                         float t;
-                        if (sphere_t(SV<C>::obj_geom(i), o, d, tmin, tmax, t)) return true;
+                        if (sphere_t(SV<C>::template obj_geom_k<K>(i), o, d, tmin, tmax, t)) return true;
                     }
                 }
             }
@@ -254,13 +254,13 @@ __device__ __forceinline__ bool run_occludes(const int4 run, V3 o, V3 d, float t
                 while (mask) {
                     const int i = c0 + __ffs(mask) - 1; mask &= mask - 1;
                     float t;
-                    if (sphere_t(SV<C>::obj_geom(i), o, d, tmin, tmax, t)) return true;
+                    if (sphere_t(SV<C>::template obj_geom_k<K>(i), o, d, tmin, tmax, t)) return true;
                 }
             }
         } else if (run.x == RUN_HALFSPACE) {
             for (int i = first; i < end; ++i) {
                 float t; ++cnt.tests;
-                if (plane_t(SV<C>::obj_geom(i), o, d, tmin, tmax, t)) return true;
+                if (plane_t(SV<C>::template obj_geom_k<K>(i), o, d, tmin, tmax, t)) return true;
             }
         } else if (K && run.w > 0) {                   // generic run with per-object world bounds: candidates only
             const int ctab = run.w - 1;
@@ -270,13 +270,13 @@ __device__ __forceinline__ bool run_occludes(const int4 run, V3 o, V3 d, float t
                 while (mask) {
                     const int i = c0 + __ffs(mask) - 1; mask &= mask - 1;
                     float t, tent; uint32_t code;
-                    if (generic_hit<C>(i, o, d, tmin, tmax, t, code, tent, cnt.tests)) return true;
+                    if (generic_hit<C, K>(i, o, d, tmin, tmax, t, code, tent, cnt.tests)) return true;
                 }
             }
         } else {
             for (int i = first; i < end; ++i) {
                 float t, tent; uint32_t code;
-                if (generic_hit<C>(i, o, d, tmin, tmax, t, code, tent, cnt.tests)) return true;
+                if (generic_hit<C, K>(i, o, d, tmin, tmax, t, code, tent, cnt.tests)) return true;
             }
         }
     }
@@ -319,7 +319,7 @@ __device__ __forceinline__ bool closest_hit(V3 o, V3 d, float tmin, float tmax, 
         hit.n = n; hit.mat = mat; hit.front = front;
         return true;
     }
-    const float4 g = SV<C>::obj_geom(best);
+    const float4 g = SV<C>::template obj_geom_k<K>(best);
     int region = 0;
     if (kind == RT_PRIM_HALFSPACE) outward = mk(g.x, g.y, g.z);
     else outward = sphere_outward<C>(g, m, o, d, best_t, region);
