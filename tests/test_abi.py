@@ -67,6 +67,32 @@ def test_png_writer_roundtrip(rt, tmp_path):
     assert e.value.code == -2
 
 
+def test_png_writer_parallel_bands_form_one_valid_zlib_stream(rt, tmp_path):
+    """Frames above 64 rows are deflated in bands on several threads; the concatenation must be ONE zlib stream (header,
+    raw-deflate bands ending on full flushes, combined Adler-32) inside one IDAT chunk with a correct CRC."""
+    import struct, zlib
+    rng = np.random.default_rng(1)
+    H, W = 1100, 700                                   # > 256 KB per band on every core count: several bands
+    img = np.zeros((H, W, 3), np.uint8)
+    img[:, :, 0] = (np.arange(W) % 256)[None, :]; img[:, :, 1] = (np.arange(H) % 256)[:, None]
+    img[::3, ::5, 2] = rng.integers(0, 256, img[::3, ::5, 2].shape, dtype=np.uint8)
+    p = str(tmp_path / "big.png")
+    rt.write_png_rgb8(p, img)
+    raw = open(p, "rb").read()
+    assert raw[:8] == b"\x89PNG\r\n\x1a\n"
+    pos, chunks = 8, []
+    while pos < len(raw):
+        n, typ = struct.unpack(">I4s", raw[pos:pos + 8])
+        data = raw[pos + 8:pos + 8 + n]
+        (crc,) = struct.unpack(">I", raw[pos + 8 + n:pos + 12 + n])
+        assert crc == zlib.crc32(typ + data) & 0xFFFFFFFF
+        chunks.append((typ, data)); pos += 12 + n
+    assert [c[0] for c in chunks] == [b"IHDR", b"IDAT", b"IEND"]
+    assert struct.unpack(">IIBBBBB", chunks[0][1]) == (W, H, 8, 2, 0, 0, 0)           # 8-bit RGB, no alpha, no interlace
+    rows = np.frombuffer(zlib.decompress(chunks[1][1]), np.uint8).reshape(H, 1 + 3 * W)   # checks the combined Adler-32 too
+    assert not rows[:, 0].any() and np.array_equal(rows[:, 1:].reshape(H, W, 3), img)
+
+
 def test_cli_usage_and_error_exit_codes(rt, tmp_path):
     cli = rt.RAY_CLI
     assert os.path.exists(cli)
