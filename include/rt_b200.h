@@ -206,6 +206,11 @@ int rt_debug_jitter(uint64_t first_sample, int n, double* out);
  * the 624 tempered outputs of block `block` (outputs 624*block .. +623) of mt19937(seed).  No GPU needed. */
 int rt_debug_mt_block_host(uint32_t seed, uint64_t block, uint32_t* out624);
 
+/* HOST restatement of the jump-ahead the checkpoint table is built with (csrc/mt19937.cuh jump_word, polynomials from
+ * csrc/mt_jump_gen.cpp): the state 2^log2_twists twists after the seeded state is obtained in ONE step, then twisted once
+ * and tempered, i.e. the result must equal rt_debug_mt_block_host(seed, 2^log2_twists, .).  No GPU needed.            */
+int rt_debug_mt_jump_host(uint32_t seed, int log2_twists, uint32_t* out624);
+
 /* HOST-ONLY view of the device layout rt_scene_upload builds (no GPU needed).  Long runs of plain spheres /
  * pokeballs are reordered spatially and get one bounding sphere per 16 primitives (the reference scans linearly,
  * scene.cpp:10-42; results are identical).  order[i] = JSON index of device object i; runs4 = (kind,

@@ -90,7 +90,7 @@ ABI_SYMBOLS = [
     "rt_init", "rt_shutdown", "rt_last_error", "rt_version",
     "rt_compile_json_text", "rt_compile_json_file", "rt_compiled_desc", "rt_compiled_free",
     "rt_scene_upload", "rt_scene_free", "rt_scene_size",
-    "rt_render", "rt_render_device", "rt_trace_rays", "rt_debug_jitter", "rt_debug_mt_block_host", "rt_debug_device_layout", "rt_debug_mask_table",
+    "rt_render", "rt_render_device", "rt_trace_rays", "rt_debug_jitter", "rt_debug_mt_block_host", "rt_debug_mt_jump_host", "rt_debug_device_layout", "rt_debug_mask_table",
     "rt_measure_fp32_peak",
     "rt_write_png_rgb8",
     "rt_peer_frame_create", "rt_peer_frame_open", "rt_peer_frame_close",
@@ -128,6 +128,7 @@ def lib():
         L.rt_trace_rays.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         L.rt_debug_jitter.argtypes = [C.c_uint64, C.c_int, C.c_void_p]
         L.rt_debug_mt_block_host.argtypes = [C.c_uint32, C.c_uint64, C.c_void_p]
+        L.rt_debug_mt_jump_host.argtypes = [C.c_uint32, C.c_int, C.c_void_p]
         L.rt_measure_fp32_peak.argtypes = [C.POINTER(C.c_double)]
         L.rt_debug_device_layout.argtypes = [C.POINTER(RtSceneDesc), C.c_void_p, C.POINTER(C.c_int), C.c_void_p, C.POINTER(C.c_int), C.c_void_p]
         L.rt_write_png_rgb8.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_int]
@@ -282,6 +283,13 @@ def debug_jitter(first_sample: int, n: int) -> np.ndarray:
 def mt_block_host(seed: int, block: int) -> np.ndarray:
     out = np.zeros(624, np.uint32)
     _check(lib().rt_debug_mt_block_host(seed, block, out.ctypes.data_as(C.c_void_p)))
+    return out
+
+
+def mt_jump_host(seed: int, log2_twists: int) -> np.ndarray:
+    """Outputs of block 2**log2_twists reached by ONE polynomial jump on the host (see rt_debug_mt_jump_host)."""
+    out = np.zeros(624, np.uint32)
+    _check(lib().rt_debug_mt_jump_host(seed, log2_twists, out.ctypes.data_as(C.c_void_p)))
     return out
 
 

@@ -54,6 +54,30 @@ inline void seed_state(uint32_t seed, uint32_t* s) {
     s[0] = seed;
     for (int i = 1; i < kN; ++i) s[i] = 1812433253u * (s[i - 1] ^ (s[i - 1] >> 30)) + (uint32_t)i;
 }
+// ---- jump ahead (see csrc/mt_jump_gen.cpp) -----------------------------------------------------------------------
+// kJumpPoly[m] = t^(624 * 2^m) mod phi: the state 2^m twists after state s is XOR_{i : bit i set} T^i s, and T^i s is
+// the window x[i .. i+623] of the word sequence that starts with s.  All coefficients are below 19937, so the first 33
+// blocks of the sequence suffice.  (Word 0 of a state only contributes its top bit; the low 31 bits of the jumped
+// state's word 0 are therefore meaningless, exactly like those of a seeded state, and nothing reads them.)
+constexpr int kJumpPolys = 32;
+constexpr int kJumpBlocks = 33;
+extern const uint32_t kJumpPoly[kJumpPolys][kN];     // generated at build time (build/mt_jump_table.cpp)
+MT_HD uint32_t jump_word(const uint32_t* x /* kJumpBlocks * kN words */, const uint32_t* poly /* kN words */, int w) {
+    uint32_t acc = 0;
+    for (int pw = 0; pw < kN; ++pw) {
+        uint32_t bits = poly[pw];
+        while (bits) {
+#if defined(__CUDA_ARCH__)
+            const int b = __ffs((int)bits) - 1;
+#else
+            const int b = __builtin_ctz(bits);
+#endif
+            bits &= bits - 1;
+            acc ^= x[32 * pw + b + w];
+        }
+    }
+    return acc;
+}
 // libstdc++ generate_canonical<double,53> + uniform_real_distribution<double>(-0.5, 0.5):
 // lo drawn first; (lo + hi*2^32) rounded to double, / 2^64, clamped below 1, then * 1.0 + (-0.5)
 MT_HD double jitter(uint32_t lo, uint32_t hi) {

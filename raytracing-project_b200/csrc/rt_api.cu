@@ -27,7 +27,8 @@ struct Context {
     cudaEvent_t ev0{nullptr}, ev1{nullptr};
     // jitter-stream checkpoints (scene independent)
     uint32_t* mt_table{nullptr}; long long mt_tiles{0}, mt_capacity{0};
-    uint32_t* mt_resume{nullptr};
+    uint32_t* mt_resume{nullptr}; long long mt_resume_tiles{0};    // sequential walk (RT_MT_SEQUENTIAL): state after mt_resume_tiles tiles
+    uint32_t* d_jump_poly{nullptr};                                // mt::kJumpPoly on the device
     unsigned long long* counters{nullptr}; unsigned* tile_counter{nullptr};
     const void* const_owner{nullptr};     // which scene currently occupies constant memory
     // frame buffers of the host-output path (rt_render): owned by the context and grown on demand, so that a
@@ -257,6 +258,7 @@ int rt_init(int device) {
     uint32_t seed[mt::kN]; mt::seed_state(12345u, seed);                  // tracer.cpp:284
     CU(cudaMemcpy(g_ctx.mt_resume, seed, sizeof(seed), cudaMemcpyHostToDevice));
     g_ctx.mt_tiles = 0; g_ctx.mt_capacity = 0; g_ctx.mt_table = nullptr; g_ctx.const_owner = nullptr;
+    g_ctx.mt_resume_tiles = 0; g_ctx.d_jump_poly = nullptr;
     CU(cudaFuncSetAttribute(rtd::render_standard_kernel<true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget));
     CU(cudaFuncSetAttribute(rtd::render_standard_kernel<true, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget));
     CU(cudaFuncSetAttribute(rtd::render_standard_kernel<true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget));
@@ -275,6 +277,7 @@ void rt_shutdown(void) {
     if (!g_ctx.ready) return;
     cudaSetDevice(g_ctx.device);
     cudaFree(g_ctx.mt_table); cudaFree(g_ctx.mt_resume); cudaFree(g_ctx.counters); cudaFree(g_ctx.tile_counter);
+    cudaFree(g_ctx.d_jump_poly); g_ctx.d_jump_poly = nullptr; g_ctx.mt_resume_tiles = 0;
     cudaFree(g_ctx.d_rgba8); cudaFree(g_ctx.d_rgbf); cudaFree(g_ctx.d_ids); cudaFree(g_ctx.d_gbuf); cudaFree(g_ctx.d_pack);
     g_ctx.d_rgba8 = nullptr; g_ctx.d_rgbf = nullptr; g_ctx.d_ids = nullptr; g_ctx.d_gbuf = nullptr; g_ctx.d_pack = nullptr;
     g_ctx.rgba8_cap = g_ctx.rgbf_cap = g_ctx.ids_cap = g_ctx.gbuf_cap = g_ctx.pack_cap = 0;
@@ -402,9 +405,41 @@ int ensure_mt_table(long long tiles) {
         cudaFree(g_ctx.mt_table);
         g_ctx.mt_table = nt; g_ctx.mt_capacity = cap;
     }
-    rtd::mt_checkpoint_kernel<<<1, 640, 0, g_ctx.stream>>>(g_ctx.mt_table, g_ctx.mt_resume, g_ctx.mt_tiles, tiles - g_ctx.mt_tiles);
-    CU(cudaGetLastError());
-    CU(cudaStreamSynchronize(g_ctx.stream));
+    const char* seq = std::getenv("RT_MT_SEQUENTIAL");            // test hook: the twist-by-twist walk from the resume state
+    if (seq && seq[0] == '1') {
+        if (g_ctx.mt_resume_tiles != g_ctx.mt_tiles) return fail(RT_ERR_STATE, "RT_MT_SEQUENTIAL: the table was built by jumps; call rt_shutdown first");
+        rtd::mt_checkpoint_kernel<<<1, 640, 0, g_ctx.stream>>>(g_ctx.mt_table, g_ctx.mt_resume, g_ctx.mt_tiles, tiles - g_ctx.mt_tiles, tiles - g_ctx.mt_tiles);
+        CU(cudaGetLastError());
+        CU(cudaStreamSynchronize(g_ctx.stream));
+        g_ctx.mt_resume_tiles = tiles;
+    } else {
+        // Segments of kSegTiles tiles (512 twists); their start states by jump-ahead, top-down: at level l the states at
+        // multiples of 2^(l+1) segments are known and give those at odd multiples of 2^l (polynomial l + 9: 2^l * 512 twists).
+        constexpr long long kSegTiles = 64;
+        constexpr int kSegLog2Twists = 9;
+        static_assert(kSegTiles * mt::kTwistsPerTile == (1ll << kSegLog2Twists), "segment length");
+        const long long n_seg = (tiles + kSegTiles - 1) / kSegTiles;
+        if (!g_ctx.d_jump_poly) {
+            CU(cudaMalloc((void**)&g_ctx.d_jump_poly, sizeof(mt::kJumpPoly)));
+            CU(cudaMemcpy(g_ctx.d_jump_poly, mt::kJumpPoly, sizeof(mt::kJumpPoly), cudaMemcpyHostToDevice));
+            CU(cudaFuncSetAttribute(rtd::mt_jump_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, rtd::kJumpSmemBytes));
+        }
+        uint32_t* seg = nullptr;
+        CU(cudaMalloc((void**)&seg, (size_t)n_seg * mt::kN * sizeof(uint32_t)));
+        uint32_t seed[mt::kN]; mt::seed_state(12345u, seed);                  // tracer.cpp:284
+        CU(cudaMemcpyAsync(seg, seed, sizeof(seed), cudaMemcpyHostToDevice, g_ctx.stream));
+        int top = 0; while ((1ll << top) < n_seg) ++top;
+        if (top + kSegLog2Twists > mt::kJumpPolys) { cudaFree(seg); return fail(RT_ERR_LIMIT, "frame too large for the jump table"); }
+        for (int l = top - 1; l >= 0; --l) {
+            const long long stride = 1ll << l, pairs = (n_seg + 2 * stride - 1) / (2 * stride);
+            rtd::mt_jump_kernel<<<(unsigned)pairs, 640, rtd::kJumpSmemBytes, g_ctx.stream>>>(g_ctx.d_jump_poly + (size_t)(l + kSegLog2Twists) * mt::kN, seg, stride, n_seg);
+        }
+        rtd::mt_checkpoint_kernel<<<(unsigned)n_seg, 640, 0, g_ctx.stream>>>(g_ctx.mt_table, seg, 0, tiles, kSegTiles);
+        cudaError_t e = cudaGetLastError();
+        if (e == cudaSuccess) e = cudaStreamSynchronize(g_ctx.stream);
+        cudaFree(seg);
+        if (e != cudaSuccess) return fail(RT_ERR_CUDA, std::string("jitter checkpoint table: ") + cudaGetErrorString(e));
+    }
     g_ctx.mt_tiles = tiles;
     return RT_OK;
 }

@@ -67,6 +67,18 @@ int rt_debug_mt_block_host(uint32_t seed, uint64_t block, uint32_t* out624) {
     return RT_OK;
 }
 
+int rt_debug_mt_jump_host(uint32_t seed, int log2_twists, uint32_t* out624) {
+    if (!out624 || log2_twists < 0 || log2_twists >= mt::kJumpPolys) { rt_set_error("rt_debug_mt_jump_host: bad argument"); return RT_ERR_ARG; }
+    std::vector<uint32_t> x((size_t)mt::kJumpBlocks * mt::kN);
+    mt::seed_state(seed, x.data());
+    for (int b = 0; b + 1 < mt::kJumpBlocks; ++b)
+        for (int k = 0; k < mt::kN; ++k) x[(size_t)(b + 1) * mt::kN + k] = mt::next_word(x.data() + (size_t)b * mt::kN, k);
+    uint32_t st[mt::kN];
+    for (int w = 0; w < mt::kN; ++w) st[w] = mt::jump_word(x.data(), mt::kJumpPoly[log2_twists], w);
+    for (int k = 0; k < mt::kN; ++k) out624[k] = mt::temper(mt::next_word(st, k));
+    return RT_OK;
+}
+
 // 8-bit RGB PNG, no alpha (main.cpp:19-34,84-89 writes CV_8UC3 through cv::imwrite), filter 0 on every row, one zlib
 // stream in one IDAT chunk.  The stream is deflated in parallel: bands of rows are compressed independently as raw deflate
 // (each ends on a full flush, the last one finishes the stream) on the host's cores, concatenated behind one zlib header,

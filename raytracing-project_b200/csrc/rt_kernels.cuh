@@ -15,22 +15,51 @@
 namespace rtd {
 
 // ---------------------------------------------------------------------------------------------------
-// MT19937 checkpoints: table[j] = state from which tile j's 8 twists start.
-__global__ void __launch_bounds__(640) mt_checkpoint_kernel(uint32_t* table, uint32_t* resume_state, long long first_tile, long long n_tiles) {
+// MT19937 checkpoints: table[j] = state from which tile j's 8 twists start.  CTA b walks `tiles_per_cta` tiles from
+// states[b] (one barrier per twist, parallel inside a twist) and leaves the state it ends on in states[b].  With one CTA
+// this is the plain sequential walk from a resume state; with one CTA per segment the segments' start states come from
+// mt_jump_kernel, and the table of a 3840x2160 frame takes ~1 ms instead of 108 ms.
+__global__ void __launch_bounds__(640) mt_checkpoint_kernel(uint32_t* table, uint32_t* states, long long first_tile, long long n_tiles,
+                                                            long long tiles_per_cta) {
     __shared__ uint32_t st[2][mt::kN];
     const int k = threadIdx.x;
-    if (k < mt::kN) st[0][k] = resume_state[k];
+    const long long t0 = (long long)blockIdx.x * tiles_per_cta;
+    if (t0 >= n_tiles) return;
+    const long long count = min(tiles_per_cta, n_tiles - t0);
+    uint32_t* state = states + (size_t)blockIdx.x * mt::kN;
+    if (k < mt::kN) st[0][k] = state[k];
     __syncthreads();
     int cur = 0;
-    for (long long j = 0; j < n_tiles; ++j) {
-        if (k < mt::kN) table[(first_tile + j) * mt::kN + k] = st[cur][k];
+    for (long long j = 0; j < count; ++j) {
+        if (k < mt::kN) table[(first_tile + t0 + j) * mt::kN + k] = st[cur][k];
         for (int b = 0; b < mt::kTwistsPerTile; ++b) {
             if (k < mt::kN) st[cur ^ 1][k] = mt::next_word(st[cur], k);
             __syncthreads();
             cur ^= 1;
         }
     }
-    if (k < mt::kN) resume_state[k] = st[cur][k];
+    if (k < mt::kN) state[k] = st[cur][k];
+}
+
+// Jump ahead (csrc/mt_jump_gen.cpp, mt::jump_word): states[src + stride] = states[src] advanced by the number of twists
+// `poly` stands for, src = 2 * stride * blockIdx.x.  One CTA per jump: the 33 blocks of the word sequence that follows the
+// source state are generated into shared memory (32 twists), then every thread XORs the windows selected by the
+// polynomial's ~10 000 set coefficients for its word (uniform control flow, conflict-free shared loads).
+constexpr int kJumpSmemBytes = (mt::kJumpBlocks + 1) * mt::kN * (int)sizeof(uint32_t);
+__global__ void __launch_bounds__(640) mt_jump_kernel(const uint32_t* __restrict__ poly, uint32_t* states, long long stride, long long n_states) {
+    extern __shared__ uint32_t jump_smem[];
+    uint32_t* x = jump_smem;
+    uint32_t* poly_s = jump_smem + mt::kJumpBlocks * mt::kN;
+    const long long src = 2 * stride * (long long)blockIdx.x, dst = src + stride;
+    if (dst >= n_states) return;
+    const int k = threadIdx.x;
+    if (k < mt::kN) { x[k] = states[src * mt::kN + k]; poly_s[k] = poly[k]; }
+    __syncthreads();
+    for (int b = 0; b + 1 < mt::kJumpBlocks; ++b) {
+        if (k < mt::kN) x[(b + 1) * mt::kN + k] = mt::next_word(x + b * mt::kN, k);
+        __syncthreads();
+    }
+    if (k < mt::kN) states[dst * mt::kN + k] = mt::jump_word(x, poly_s, k);
 }
 
 // First n jitter pairs from sample `first` using the same tile machinery (debug / known-answer).

@@ -87,6 +87,22 @@ def test_jitter_stream_is_bit_exact(gpu, oa):
         assert np.array_equal(gpu.debug_jitter(first, n), oa.jitter(first, n)), (first, n)
 
 
+def test_checkpoint_table_by_jumps_equals_the_sequential_walk(gpu, oa, monkeypatch):
+    """The checkpoint table is built by GF(2) jump-ahead (segment start states) + short parallel walks; RT_MT_SEQUENTIAL=1
+    forces the twist-by-twist walk from the seed.  Both must give the same stream, also when the table grows."""
+    probes = [(0, 3000), (64 * 1248 - 7, 40), (1248 * 777 + 3, 2500), (40_000_000, 1500)]
+    out = {}
+    for force in ("1", "0"):
+        gpu.shutdown()
+        monkeypatch.setenv("RT_MT_SEQUENTIAL", force)
+        gpu.init(0)
+        out[force] = [gpu.debug_jitter(first, n) for first, n in probes]          # the table grows from probe to probe
+    monkeypatch.delenv("RT_MT_SEQUENTIAL")
+    for (first, n), a, b in zip(probes, out["1"], out["0"]):
+        assert np.array_equal(a, b), (first, n)
+        assert np.array_equal(b, oa.jitter(first, n)), (first, n)
+
+
 @pytest.mark.parametrize("mode", ["standard", "paper"])
 @pytest.mark.parametrize("world", [2, 3])
 def test_sharded_render_equals_whole_frame(gpu, mode, world):

@@ -36,6 +36,18 @@ def test_product_block_generator_on_host(rt, oa):
     assert np.array_equal(rt.mt_block_host(5489, 0), np.random.RandomState(5489)._bit_generator.random_raw(624).astype(np.uint32))
 
 
+def test_jump_polynomials_on_host(rt, oa):
+    """t^(624 * 2^m) mod phi (generated at build time by csrc/mt_jump_gen.cpp) applied to the seeded state in ONE step
+    (csrc/mt19937.cuh jump_word, the code the checkpoint-table kernel runs) lands where 2^m twists land."""
+    for m in range(0, 13):
+        assert np.array_equal(rt.mt_jump_host(12345, m), rt.mt_block_host(12345, 1 << m)), m
+    for seed, m in ((12345, 17), (5489, 15)):
+        assert np.array_equal(rt.mt_jump_host(seed, m), oa.mt_raw(seed, 624 * (1 << m), 624)), (seed, m)
+    rs = np.random.RandomState(777)                                   # an independent MT19937 (numpy legacy seeding = init_genrand)
+    raw = rs._bit_generator.random_raw(624 * 1025).astype(np.uint32)
+    assert np.array_equal(rt.mt_jump_host(777, 10), raw[624 * 1024:])
+
+
 def test_discard_is_position_independent(oa):
     a = oa.jitter(1000, 50)
     b = oa.jitter(0, 1050)[1000:]
