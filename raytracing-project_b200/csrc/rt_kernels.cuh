@@ -410,8 +410,12 @@ struct GBuf { float t, nx, ny, nz; int mat; float lum; int code; int hit; };   /
 constexpr int kPaperRows = 16;
 __device__ __host__ __forceinline__ bool paper_row_owned(int y, int rank, int world) { return ((y / kPaperRows) % world) == rank; }
 
+// 3 CTAs per SM (80 registers): penguin 4K 1.17 -> 1.12 ms, snorlax 4K --paper 2.26 -> 2.05 ms; 4 (64 registers) spills back to 1.16 / 2.20
+#ifndef RT_PAPER_BLOCKS
+#define RT_PAPER_BLOCKS 3
+#endif
 template <bool C, bool K>
-__global__ void __launch_bounds__(256) paper_gbuffer_kernel(GBuf* gb, int* ids, unsigned long long* counters, int rank, int world) {
+__global__ void __launch_bounds__(256, RT_PAPER_BLOCKS) paper_gbuffer_kernel(GBuf* gb, int* ids, unsigned long long* counters, int rank, int world) {
     const int nx = c_hdr.nx, ny = c_hdr.ny;
     const long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     Counters cnt = {0, 0, 0, 0};

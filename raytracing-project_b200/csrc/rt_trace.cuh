@@ -340,7 +340,9 @@ __device__ __forceinline__ bool occluded(V3 o, V3 d, float tmin, float tmax, Cou
         return sr.best >= 0;
     }
     const int n_runs = c_hdr.n_runs;
-    for (int r = 0; r < n_runs; ++r)
+    // any-hit: the order of the scan cannot be observed (scene.cpp:33-42 returns a bool); the runs are walked backwards
+    // because later objects are usually the foreground detail that casts the shadows (snorlax 4K -0.3 %, synthetic-B -1.2 %)
+    for (int r = n_runs - 1; r >= 0; --r)
         if (run_occludes<C, K>(SV<C>::run(r), o, d, tmin, tmax, cnt)) return true;
     return false;
 }
