@@ -387,6 +387,47 @@ __device__ __forceinline__ void light_term(int l, const float4 m0, float ks, flo
     E = screen(E, screen(Ed, Es));
 }
 
+// The same term in two halves, for trace_flat: the shadow query first (light_visible), the contribution later (light_shade;
+// the light vector is recomputed, 15 instructions), so that no shading state is live across the scans of a flat scene.
+__device__ __forceinline__ float light_vector(float4 lp, V3 p, V3 n, V3& wi, float& dist) {
+    V3 L = mk(lp.x - p.x, lp.y - p.y, lp.z - p.z);
+    float d2 = fmaxf(dot(L, L), 0.01f);
+    dist = sqrtf(d2);
+    float inv = 1.f / dist;
+    wi = mk(L.x * inv, L.y * inv, L.z * inv);
+    return fmaxf(0.f, dot(n, wi));
+}
+template <bool C, bool K>
+__device__ __forceinline__ bool light_visible(int l, V3 n, V3 p, V3 so, float eps, Counters& cnt) {
+    V3 wi; float dist;
+    const float ndotl = light_vector(SV<C>::light(l, 0), p, n, wi, dist);
+    if (ndotl <= 0.f) return false;
+    const float tmaxS = dist - eps;
+    if (tmaxS <= eps) return false;
+    ++cnt.shadow;
+    return !occluded<C, K>(so, normalized(wi), eps, tmaxS, cnt);               // Ray ctor re-normalises (core.h:278)
+}
+template <bool C>
+__device__ __forceinline__ void light_shade(int l, const float4 m0, float ks, float shininess, float kd, V3 n, V3 p, V3 wo, RGBf& E) {
+    const float4 li = SV<C>::light(l, 1);
+    V3 wi; float dist;
+    const float ndotl = light_vector(SV<C>::light(l, 0), p, n, wi, dist);
+    float eff = fmaxf(0.5f, dist);
+    float fall = 2.0f / (eff * eff);                                         // falloff * 2.0 (shading.cpp:108-112)
+    RGBf I = rgb(li.x * fall, li.y * fall, li.z * fall);
+    float kdn = kd * ndotl * 1.5f;                                           // shading.cpp:115
+    RGBf Ed = rgb(m0.x * I.r * kdn, m0.y * I.g * kdn, m0.z * I.b * kdn);
+    RGBf Es = rgb(0.f, 0.f, 0.f);
+    if (ks > 0.f) {                                                          // shading.cpp:118-126
+        float two = 2.f * dot(n, wi);
+        V3 rr = normalized(mk(fmaf(two, n.x, -wi.x), fmaf(two, n.y, -wi.y), fmaf(two, n.z, -wi.z)));
+        float rdotv = fmaxf(0.f, dot(rr, wo));
+        float spec = (rdotv > 0.f ? __powf(rdotv, shininess) : powf(rdotv, shininess)) * ks;
+        Es = rgb(I.r * spec, I.g * spec, I.b * spec);
+    }
+    E = screen(E, screen(Ed, Es));
+}
+
 template <bool C, bool K>
 __device__ RGBf shade(const Hit& h, V3 p, V3 wo, Counters& cnt) {
     if (h.mat < 0) return rgb(1.f, 0.f, 1.f);                                // shading.cpp:33
@@ -413,16 +454,26 @@ __device__ RGBf trace_flat(bool active, bool lockstep, V3 o, V3 d, Hit& primary,
     primary = h; primary_hit = hit;
     const bool lit = hit && h.mat >= 0;
     const V3 p = madd(o, d, h.t);
-    const V3 wo = normalized(neg(d));
-    float4 m0 = make_float4(0.f, 0.f, 0.f, 0.f), m1 = m0, m2 = m0;
-    if (lit) { m0 = material(h.mat, 0); m1 = material(h.mat, 1); m2 = material(h.mat, 2); }
-    RGBf E = rgb(m1.x, m1.y, m1.z);
     const float eps = fmaxf(1e-3f, 1e-4f * h.t);
     const V3 so = madd(p, h.n, eps);
     const int nl = c_hdr.n_lights;
-    for (int l = 0; l < nl; ++l) {
-        if (lockstep) __syncthreads();
-        if (lit) light_term<C, K>(l, m0, m0.w, m2.y, m2.w, h.n, p, so, wo, eps, E, cnt);
+    RGBf E = rgb(0.f, 0.f, 0.f);
+    for (int l0 = 0; l0 < nl || l0 == 0; l0 += 32) {              // lights in chunks of 32: one visibility bit each
+        const int cnt_l = min(32, nl - l0);
+        uint32_t vis = 0;
+        for (int k = 0; k < cnt_l; ++k) {
+            if (lockstep) __syncthreads();
+            if (lit) vis |= light_visible<C, K>(l0 + k, h.n, p, so, eps, cnt) ? (1u << k) : 0u;
+        }
+        if (lit) {
+            const float4 m0 = material(h.mat, 0), m2 = material(h.mat, 2);
+            if (l0 == 0) { const float4 m1 = material(h.mat, 1); E = rgb(m1.x, m1.y, m1.z); }   // ambient, pre-multiplied
+            const V3 wo = normalized(neg(d));
+            while (vis) {
+                const int k = __ffs(vis) - 1; vis &= vis - 1;
+                light_shade<C>(l0 + k, m0, m0.w, m2.y, m2.w, h.n, p, wo, E);
+            }
+        }
     }
     if (!hit) return rgb(c_hdr.bg[0], c_hdr.bg[1], c_hdr.bg[2]);             // tracer.cpp:72
     if (!lit) return rgb(1.f, 0.f, 1.f);                                     // shading.cpp:33
