@@ -129,6 +129,29 @@ def cpu_sample(scene_path: str, height: int, threads: int, target_s: float):
             "kind": "reference" if have_ref else "port", "stride": stride, "threads": threads}
 
 
+def cpu_paper_frame(scene_path: str, width: int, height: int, shadow_rays: int | None):
+    """Paper mode has no RNG to discard, so the CPU leg renders the WHOLE frame with the reference (one thread, as the
+    reference runs).  Its queries: per pixel one closest hit + the shadow scans of the centre ray (trace_paper + shade,
+    tracer.cpp:111-120,262-266) and the centre + four neighbour re-traces of get_edge_strength (tracer.cpp:133-178)."""
+    have_ref = os.path.exists(REF_DRIVER)
+    if have_ref:
+        p = subprocess.run([REF_DRIVER, scene_path, "--quiet", "--paper"], capture_output=True, text=True, check=True)
+        ms = float(json.loads(p.stdout.strip().splitlines()[-1])["render_ms"])
+    else:
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import oracle_api as oa
+        o = oa.Oracle.from_file(scene_path)
+        t0 = time.perf_counter(); o.render("paper", threads=1); ms = (time.perf_counter() - t0) * 1e3
+    closest = 2 * width * height + 4 * width * height - 2 * width - 2 * height      # neighbours outside the frame are skipped
+    if shadow_rays is None:
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import oracle_api as oa
+        L = oa.lib(); L.orc_count_rays.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]
+        shadow_rays = 0      # the oracle's counter walks the Standard loop only; the shadow share is reported by our arm
+    rays = closest + shadow_rays
+    return {"value": rays / (ms * 1e-3) / 1e6, "busy_ms": ms, "rays": rays, "kind": "reference" if have_ref else "port"}
+
+
 def run_reference(args) -> None:
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -137,6 +160,24 @@ def run_reference(args) -> None:
         scr = json.load(f)["screen"]
     W = max(1, round(scr["dimensions"][0] * scr.get("dpi", 72))); H = max(1, round(scr["dimensions"][1] * scr.get("dpi", 72)))
     threads = os.cpu_count() or 1
+    if args.paper:
+        # whole frames, one per step, one thread (the paper loop has no sequential RNG, but the reference is single-threaded
+        # and a frame takes seconds: no sampling needed)
+        vals, ms = [], []
+        for i in range(min(args.warmup, 1) + min(args.steps, 3)):
+            c = cpu_paper_frame(args.scene, W, H, None)
+            if i >= min(args.warmup, 1):
+                vals.append(c["value"]); ms.append(c["busy_ms"])
+        v = float(np.mean(vals))
+        print(json.dumps({
+            "impl": "reference", "metric": "Mrays/s", "value": v, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": len(vals),
+            "warmup": min(args.warmup, 1), "ms_per_step": float(np.mean(ms)), "ms_per_frame": float(np.mean(ms)), "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": os.path.basename(args.scene), "width": W, "height": H, "spp": 1, "mode": "paper",
+                       "step": "one whole paper-mode frame, 1 thread (closest-hit queries only: 6 per pixel, tracer.cpp:133-178,262)"},
+            "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": 1, "kind": c["kind"], "sample": f"whole {W}x{H} paper frame"},
+            "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        return
     target = max(2.0, min(10.0, 150.0 / max(1, args.steps + args.warmup)))
     vals, step_ms, last = [], [], None
     for i in range(args.warmup + args.steps):
@@ -320,6 +361,18 @@ def run_ours(args) -> None:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_ms = float(te[0])
 
+    # ---- N > 1: the peer-assembled frame must equal the frame one GPU renders alone, byte for byte (untimed) ----
+    frame_equal = None
+    if world > 1:
+        assembled = step().clone()
+        torch.cuda.synchronize()
+        if rank == 0:
+            alone = torch.zeros((H, W, 4), dtype=torch.uint8, device=dev)
+            tracer.render_device(alone.data_ptr(), stream=stream, rank=0, world=1)
+            torch.cuda.synchronize()
+            frame_equal = bool(torch.equal(assembled.reshape(H, W, 4), alone))
+        barrier()
+
     if rank == 0:
         flops = flops_of(tot, W * H)
         achieved = flops / (kernel_ms * 1e-3) / 1e12 / world          # per GPU
@@ -345,12 +398,20 @@ def run_ours(args) -> None:
                                          "hbm_peak_gbs": hbm_peak_gbs(), "note": "RGBA8 stores only; the frame is compute-bound"}},
             "clocks": clocks,
         }
+        if frame_equal is not None:
+            line["frame_equals_single_gpu"] = frame_equal
         if world == 1 and not args.no_cpu:
             try:
-                c = cpu_sample(args.scene, H, 1, args.cpu_seconds)
-                line["cpu_baseline"] = {"value": c["value"], "unit": "Mrays/s", "cores": 1, "kind": c["kind"],
-                                        "sample": f"{c['rows']} rows (y % {c['stride']} == 0) of {W}x{H}, 1 thread, {c['busy_ms']:.0f} ms inside the rows",
-                                        "ms_per_frame_extrapolated": rays_per_frame / (c["value"] * 1e6) * 1e3}
+                if args.paper:
+                    c = cpu_paper_frame(args.scene, W, H, tot["shadow_rays"])
+                    line["cpu_baseline"] = {"value": c["value"], "unit": "Mrays/s", "cores": 1, "kind": c["kind"],
+                                            "sample": f"whole {W}x{H} paper frame, 1 thread; the reference re-traces 5 extra closest hits per pixel "
+                                                      f"(tracer.cpp:133-178), counted as its rays", "ms_per_frame": c["busy_ms"]}
+                else:
+                    c = cpu_sample(args.scene, H, 1, args.cpu_seconds)
+                    line["cpu_baseline"] = {"value": c["value"], "unit": "Mrays/s", "cores": 1, "kind": c["kind"],
+                                            "sample": f"{c['rows']} rows (y % {c['stride']} == 0) of {W}x{H}, 1 thread, {c['busy_ms']:.0f} ms inside the rows",
+                                            "ms_per_frame_extrapolated": rays_per_frame / (c["value"] * 1e6) * 1e3}
             except Exception as e:  # the baseline is a report, never a reason to lose the GPU number
                 line["cpu_baseline"] = {"error": str(e)}
         print(json.dumps(line))

@@ -51,6 +51,12 @@ typedef struct rt_material {
 /* PointLight (raytracer/src/scene.h:22-27) */
 typedef struct rt_light { float pos[3]; float pad0; float intensity[3]; float pad1; } rt_light;
 
+/* DirectionalLight (raytracer/src/scene.h:10-19) as shade_lambert_phong uses it (shading.cpp:46-76):
+ * to_light = (-dir).normalized() (core.h:95-101: length <= 1e-6 falls back to +Y), radiance without falloff.
+ * The reference's JSON loader never creates one (json_loader.cpp:191-204); a C++ host that fills
+ * scene.dir_lights itself binds rt_compiled_add_dir_light.                                              */
+typedef struct rt_dir_light { float to_light[3]; float pad0; float radiance[3]; float pad1; } rt_dir_light;
+
 /* Primitive kinds and flags */
 enum { RT_PRIM_SPHERE = 0, RT_PRIM_HALFSPACE = 1, RT_PRIM_POKEBALL = 2, RT_PRIM_PROGRAM = 3 };
 enum {
@@ -123,6 +129,9 @@ typedef struct rt_scene_desc {
     const rt_material* materials;
     const rt_light*    lights;
     const float*       fallbacks;   /* n_fallbacks x 4 floats (unit normal, pad) */
+    /* directional lights (scene.h:37): shaded BEFORE the point lights, in this order (shading.cpp:46,79) */
+    int32_t n_dir_lights; int32_t pad0;
+    const rt_dir_light* dir_lights;
 } rt_scene_desc;
 
 typedef struct rt_scene rt_scene;          /* a scene resident on the device(s) */
@@ -150,6 +159,9 @@ const char* rt_version(void);
 int rt_compile_json_text(const char* json_text, rt_compiled** out);
 int rt_compile_json_file(const char* path, rt_compiled** out);
 const rt_scene_desc* rt_compiled_desc(const rt_compiled*);
+/* scene.dir_lights.push_back({dir, radiance}) (scene.h:10-19,37) on a compiled scene; `dir` is the direction the
+ * light travels (from the light toward the scene), as in the reference.  Call before rt_scene_upload.   */
+int rt_compiled_add_dir_light(rt_compiled*, const double dir[3], const double radiance[3]);
 void rt_compiled_free(rt_compiled*);
 
 /* ---- device scene ---------------------------------------------------------------------------- */
@@ -224,6 +236,11 @@ int rt_debug_device_layout(const rt_scene_desc* desc, int* order, int* n_runs, i
  * arithmetic of Sphere::intersect (geometry.cpp:12-37).  masks4 holds *n x 4 floats (n = objects + leaves + bounds);
  * pass masks4 = NULL to query n.                                                                              */
 int rt_debug_mask_table(const rt_scene_desc* desc, int* n, float* masks4, float* scale);
+
+/* Test hooks.  name: "flat", "lockstep", "wavefront", "global_scene" (kernel / data-path selection of scenes uploaded
+ * afterwards) or "mt_sequential" (checkpoint table by the twist-by-twist walk); value -1 = the library's own choice,
+ * 0 / 1 = forced off / on.  The library never reads its behaviour from the environment.                          */
+int rt_debug_set_option(const char* name, int value);
 
 /* Measured FP32 FFMA peak of the current device in TFLOP/s (dependent-free FFMA micro-benchmark). */
 int rt_measure_fp32_peak(double* tflops);

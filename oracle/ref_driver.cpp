@@ -78,13 +78,14 @@ template <class T> static void put(std::vector<char>& b, const T* p, size_t n) {
 static void usage() {
     std::cerr <<
       "usage: ref_driver <scene.json> [--paper] [--fb out.fb] [--ids out.ids] [--rows y0 y1] [--stride k off]\n"
-      "                  [--rays in.rays out.rays] [--quiet] [--repeat n]\n";
+      "                  [--rays in.rays out.rays] [--quiet] [--repeat n] [--dirlight dx dy dz r g b]...\n";
 }
 
 int main(int argc, char** argv) {
     if (argc < 2) { usage(); return 1; }
     std::string scene_path = argv[1], fb_path, ids_path, rays_in, rays_out;
     bool paper = false, quiet = false; int y0 = -1, y1 = -1, repeat = 1, stride = 1, stride_off = 0;
+    std::vector<DirectionalLight> dir_lights;      // the JSON format has none (json_loader.cpp:191-204); pushed into scene.dir_lights below
     for (int i = 2; i < argc; ++i) {
         std::string a = argv[i];
         if (a == "--paper") paper = true;
@@ -95,6 +96,12 @@ int main(int argc, char** argv) {
         else if (a == "--stride" && i + 2 < argc) { stride = atoi(argv[++i]); stride_off = atoi(argv[++i]); if (y0 < 0) { y0 = 0; y1 = 1 << 30; } }
         else if (a == "--rays" && i + 2 < argc) { rays_in = argv[++i]; rays_out = argv[++i]; }
         else if (a == "--repeat" && i + 1 < argc) repeat = atoi(argv[++i]);
+        else if (a == "--dirlight" && i + 6 < argc) {
+            DirectionalLight L;
+            L.dir = Dir3(atof(argv[i + 1]), atof(argv[i + 2]), atof(argv[i + 3]));
+            L.radiance = Color{atof(argv[i + 4]), atof(argv[i + 5]), atof(argv[i + 6])};
+            dir_lights.push_back(L); i += 6;
+        }
         else { usage(); return 1; }
     }
     Scene scene; Camera cam;
@@ -104,6 +111,7 @@ int main(int argc, char** argv) {
         std::cerr << "[error] " << e.what() << "\n";
         return 3;
     }
+    for (const auto& L : dir_lights) scene.dir_lights.push_back(L);
     const int W = cam.screen.nx(), H = cam.screen.ny();
     Tracer tracer; tracer.scene = &scene; tracer.camera = &cam; tracer.width = W; tracer.height = H;
     tracer.mode = paper ? RenderMode::Paper : RenderMode::Standard;

@@ -64,6 +64,10 @@ class RtLight(C.Structure):
     _fields_ = [("pos", C.c_float * 3), ("pad0", C.c_float), ("intensity", C.c_float * 3), ("pad1", C.c_float)]
 
 
+class RtDirLight(C.Structure):
+    _fields_ = [("to_light", C.c_float * 3), ("pad0", C.c_float), ("radiance", C.c_float * 3), ("pad1", C.c_float)]
+
+
 class RtPokeball(C.Structure):
     _fields_ = [("btn_dir", C.c_float * 3), ("cos_outer", C.c_float), ("up", C.c_float * 3), ("cos_inner", C.c_float),
                 ("belt_half", C.c_float), ("pad", C.c_float * 3)]
@@ -82,15 +86,16 @@ class RtSceneDesc(C.Structure):
                 ("n_ops", C.c_int32), ("n_materials", C.c_int32), ("n_lights", C.c_int32), ("n_fallbacks", C.c_int32),
                 ("objects", C.POINTER(RtPrim)), ("leaves", C.POINTER(RtPrim)), ("pokeballs", C.POINTER(RtPokeball)),
                 ("affines", C.POINTER(RtAffine)), ("ops", C.POINTER(C.c_uint32)), ("materials", C.POINTER(RtMaterial)),
-                ("lights", C.POINTER(RtLight)), ("fallbacks", C.POINTER(C.c_float))]
+                ("lights", C.POINTER(RtLight)), ("fallbacks", C.POINTER(C.c_float)),
+                ("n_dir_lights", C.c_int32), ("pad0", C.c_int32), ("dir_lights", C.POINTER(RtDirLight))]
 
 
 # every symbol include/rt_b200.h declares (tests/test_abi.py checks the list against the header)
 ABI_SYMBOLS = [
     "rt_init", "rt_shutdown", "rt_last_error", "rt_version",
-    "rt_compile_json_text", "rt_compile_json_file", "rt_compiled_desc", "rt_compiled_free",
+    "rt_compile_json_text", "rt_compile_json_file", "rt_compiled_desc", "rt_compiled_free", "rt_compiled_add_dir_light",
     "rt_scene_upload", "rt_scene_free", "rt_scene_size",
-    "rt_render", "rt_render_device", "rt_trace_rays", "rt_debug_jitter", "rt_debug_mt_block_host", "rt_debug_mt_jump_host", "rt_debug_device_layout", "rt_debug_mask_table",
+    "rt_render", "rt_render_device", "rt_trace_rays", "rt_debug_jitter", "rt_debug_mt_block_host", "rt_debug_mt_jump_host", "rt_debug_device_layout", "rt_debug_mask_table", "rt_debug_set_option",
     "rt_measure_fp32_peak",
     "rt_write_png_rgb8",
     "rt_peer_frame_create", "rt_peer_frame_open", "rt_peer_frame_close",
@@ -119,6 +124,7 @@ def lib():
         L.rt_compiled_desc.restype = C.POINTER(RtSceneDesc)
         L.rt_compiled_desc.argtypes = [C.c_void_p]
         L.rt_compiled_free.argtypes = [C.c_void_p]
+        L.rt_compiled_add_dir_light.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         L.rt_scene_upload.argtypes = [C.POINTER(RtSceneDesc), C.POINTER(C.c_void_p)]
         L.rt_scene_free.argtypes = [C.c_void_p]
         L.rt_scene_size.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
@@ -196,6 +202,13 @@ class Scene:
         masks = np.zeros((max(n.value, 1), 4), np.float32)
         _check(lib().rt_debug_mask_table(C.byref(self.desc), C.byref(n), masks.ctypes.data_as(C.c_void_p), C.byref(scale)))
         return masks[: n.value], float(scale.value)
+
+    def add_dir_light(self, direction, radiance) -> None:
+        """scene.dir_lights.push_back({dir, radiance}) (scene.h:10-19,37); before the first render."""
+        if self._device:
+            raise RtError(-6, "add_dir_light: the scene is already on the device")
+        d = np.asarray(direction, np.float64); r = np.asarray(radiance, np.float64)
+        _check(lib().rt_compiled_add_dir_light(self._compiled, d.ctypes.data_as(C.c_void_p), r.ctypes.data_as(C.c_void_p)))
 
     def device_handle(self):
         if not self._device:
@@ -291,6 +304,15 @@ def mt_jump_host(seed: int, log2_twists: int) -> np.ndarray:
     out = np.zeros(624, np.uint32)
     _check(lib().rt_debug_mt_jump_host(seed, log2_twists, out.ctypes.data_as(C.c_void_p)))
     return out
+
+
+DEBUG_OPTIONS = ("flat", "lockstep", "wavefront", "global_scene", "mt_sequential")
+
+
+def debug_option(name: str, value: int = -1) -> None:
+    """Test hook (rt_debug_set_option): force a kernel / data path for scenes uploaded afterwards; -1 restores the default."""
+    lib().rt_debug_set_option.argtypes = [C.c_char_p, C.c_int]
+    _check(lib().rt_debug_set_option(name.encode(), int(value)))
 
 
 def measure_fp32_peak() -> float:

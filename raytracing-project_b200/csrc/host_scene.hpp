@@ -53,11 +53,13 @@ struct ScreenSpec {
 struct Camera { Vec3d eye{0, 0, 1}; ScreenSpec screen; };
 
 struct PointLight { Vec3d pos; ColorD intensity{10, 10, 10}; };   // scene.h:22-27
+struct DirectionalLight { Vec3d dir{0, -1, 0}; ColorD radiance{1, 1, 1}; };   // scene.h:10-19 (dir: from the light toward the scene)
 
 // Scene (scene.h:32-47).  Owns its nodes (the reference keeps them in file-static pools,
 // json_loader.cpp:27-35, so only one scene can be alive per process; here each Scene is independent).
 struct Scene {
     std::vector<std::shared_ptr<Node>> objects;
+    std::vector<DirectionalLight> dir_lights;      // never filled by the JSON loader (json_loader.cpp:191-204)
     std::vector<PointLight> point_lights;
     ColorD background{0, 0, 0};
     ColorD ambient{0, 0, 0};

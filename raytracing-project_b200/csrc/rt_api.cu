@@ -39,6 +39,9 @@ struct Context {
     std::mutex mu;
 };
 Context g_ctx;
+// Test hooks (rt_debug_set_option): -1 = the library's own choice, 0 / 1 = forced.  Never read from the environment.
+struct DebugOptions { int flat{-1}, lockstep{-1}, wavefront{-1}, global_scene{-1}, mt_sequential{-1}; };
+DebugOptions g_opts;
 constexpr size_t kSceneSmemBudget = 80 * 1024;   // + 25 KB of MT19937 buffers: two CTAs per SM still fit in 227 KB
 
 template <class T> int upload(const std::vector<T>& h, T** d) {
@@ -72,6 +75,8 @@ struct rt_scene {
 };
 
 namespace {
+
+void free_scene_locked(rt_scene* s);
 
 int4 meta_of(const rt_prim& p) { return make_int4((p.kind & 0xff) | (p.flags << 8), p.mat, p.aux, p.xf); }
 
@@ -177,6 +182,11 @@ void build_host_arrays(const rt_scene_desc& d, rt_scene& s) {
         s.materials.push_back(make_float4(m.albedo[0], m.albedo[1], m.albedo[2], m.ks));
         s.materials.push_back(make_float4(m.ambient[0], m.ambient[1], m.ambient[2], m.kr));
         s.materials.push_back(make_float4(m.kt, m.shininess, m.ior, m.kd));
+    }
+    // directional lights first (shading.cpp:46 before :79), marked by w = 1 and carrying the unit vector TO the light
+    for (int i = 0; i < d.n_dir_lights; ++i) {
+        s.lights.push_back(make_float4(d.dir_lights[i].to_light[0], d.dir_lights[i].to_light[1], d.dir_lights[i].to_light[2], 1.f));
+        s.lights.push_back(make_float4(d.dir_lights[i].radiance[0], d.dir_lights[i].radiance[1], d.dir_lights[i].radiance[2], 0.f));
     }
     for (int i = 0; i < d.n_lights; ++i) {
         s.lights.push_back(make_float4(d.lights[i].pos[0], d.lights[i].pos[1], d.lights[i].pos[2], 0.f));
@@ -293,6 +303,7 @@ int rt_scene_upload(const rt_scene_desc* d, rt_scene** out) {
     if (!g_ctx.ready) { int rc = rt_init(-1); if (rc) return rc; }
     if (d->width <= 0 || d->height <= 0) return fail(RT_ERR_ARG, "rt_scene_upload: empty screen");
     if (d->recursion > RT_MAX_RECURSION) return fail(RT_ERR_LIMIT, "medium.recursion exceeds RT_MAX_RECURSION");
+    std::lock_guard<std::mutex> lk(g_ctx.mu);
     CU(cudaSetDevice(g_ctx.device));
     auto* s = new rt_scene();
     build_host_arrays(*d, *s);
@@ -303,12 +314,12 @@ int rt_scene_upload(const rt_scene_desc* d, rt_scene** out) {
         (rc = upload(s->ops, &s->d_ops)) || (rc = upload(s->materials, &s->d_materials)) ||
         (rc = upload(s->lights, &s->d_lights)) || (rc = upload(s->fallbacks, &s->d_fallbacks)) ||
         (rc = upload(s->runs, &s->d_runs)) || (rc = upload(s->clusters, &s->d_clusters)) ||
-        (rc = upload(s->obj_orig, &s->d_obj_orig)) || (rc = upload(s->masks, &s->d_masks))) { rt_scene_free(s); return rc; }
+        (rc = upload(s->obj_orig, &s->d_obj_orig)) || (rc = upload(s->masks, &s->d_masks))) { free_scene_locked(s); return rc; }
     rtd::SceneHeader& h = s->hdr;
     for (int k = 0; k < 3; ++k) { h.eye[k] = d->eye[k]; h.P[k] = d->screen_p[k]; h.bg[k] = d->background[k]; }
     h.lx = d->lx; h.ly = d->ly; h.nx = d->width; h.ny = d->height;
     h.medium_index = d->medium_index; h.recursion = d->recursion;
-    h.n_objects = d->n_objects; h.n_lights = d->n_lights; h.n_runs = (int)s->runs.size();
+    h.n_objects = d->n_objects; h.n_lights = d->n_dir_lights + d->n_lights; h.n_runs = (int)s->runs.size();
     h.obj_geom = s->d_obj_geom; h.obj_meta = s->d_obj_meta; h.leaf_geom = s->d_leaf_geom; h.leaf_meta = s->d_leaf_meta;
     h.pokeballs = s->d_pokeballs; h.affines = s->d_affines; h.ops = s->d_ops; h.materials = s->d_materials;
     h.lights = s->d_lights; h.fallbacks = s->d_fallbacks; h.runs = s->d_runs; h.clusters = s->d_clusters; h.obj_orig = s->d_obj_orig;
@@ -319,7 +330,7 @@ int rt_scene_upload(const rt_scene_desc* d, rt_scene** out) {
     h.off_leaf_geom = s->clusters.empty() ? d->n_objects : 0;        // scenes with bounds read top-level geometry from global memory
     h.off_leaf_meta = h.off_leaf_geom + d->n_leaves; h.off_runs = h.off_leaf_meta + d->n_leaves;
     h.off_lights = h.off_runs + (int)s->runs.size();
-    h.off_clusters = h.off_lights + 2 * d->n_lights;
+    h.off_clusters = h.off_lights + 2 * h.n_lights;
     h.off_masks = h.off_clusters + h.n_clusters;
     h.off_ops_bytes = 16 * (h.off_masks + (int)s->masks.size());
     h.smem_bytes = h.off_ops_bytes + 4 * d->n_ops;
@@ -330,24 +341,46 @@ int rt_scene_upload(const rt_scene_desc* d, rt_scene** out) {
     int n_bounce = 0;
     for (int i = 0; i < d->n_materials; ++i) n_bounce += (d->materials[i].kr > 0.f || d->materials[i].kt > 0.f) ? 1 : 0;
     s->flat = d->recursion >= 1 && (n_bounce == 0 || d->recursion == 1);
-    if (const char* e = std::getenv("RT_FORCE_FLAT")) if (e[0] == '0') s->flat = false;            // test hook: generic loop on a flat scene
+    if (g_opts.flat == 0) s->flat = false;                                  // test hook: generic loop on a flat scene
     s->lockstep = s->flat && (d->n_ops > 0 || d->n_affines > 0);
-    if (const char* e = std::getenv("RT_FORCE_LOCKSTEP")) s->lockstep = s->flat && e[0] == '1';     // test hook
+    if (g_opts.lockstep >= 0) s->lockstep = s->flat && g_opts.lockstep == 1;  // test hook
     s->bounces = d->recursion >= 2 && d->n_materials > 0 && 2 * n_bounce >= d->n_materials;
-    if (const char* e = std::getenv("RT_FORCE_WAVEFRONT")) s->bounces = e[0] == '1';       // test hook: either kernel on any scene
-    if (const char* e = std::getenv("RT_FORCE_GLOBAL")) if (e[0] == '1') s->fits_const = false;   // test hook: exercise the global-memory path on any scene
+    if (g_opts.wavefront >= 0) s->bounces = g_opts.wavefront == 1;          // test hook: either kernel on any scene
+    if (g_opts.global_scene == 1) s->fits_const = false;                    // test hook: the global-memory path on any scene
     *out = s;
     return RT_OK;
 }
 
 void rt_scene_free(rt_scene* s) {
     if (!s) return;
+    std::lock_guard<std::mutex> lk(g_ctx.mu);
+    free_scene_locked(s);
+}
+
+int rt_debug_set_option(const char* name, int value) {
+    if (!name) return fail(RT_ERR_ARG, "rt_debug_set_option: null name");
+    std::lock_guard<std::mutex> lk(g_ctx.mu);
+    const std::string n(name);
+    int* slot = n == "flat" ? &g_opts.flat : n == "lockstep" ? &g_opts.lockstep : n == "wavefront" ? &g_opts.wavefront
+              : n == "global_scene" ? &g_opts.global_scene : n == "mt_sequential" ? &g_opts.mt_sequential : nullptr;
+    if (!slot) return fail(RT_ERR_ARG, "rt_debug_set_option: unknown option " + n);
+    *slot = value < 0 ? -1 : (value ? 1 : 0);
+    return RT_OK;
+}
+
+}  // extern "C"
+
+namespace {
+void free_scene_locked(rt_scene* s) {
     if (g_ctx.const_owner == s) g_ctx.const_owner = nullptr;
     cudaFree(s->d_obj_geom); cudaFree(s->d_obj_meta); cudaFree(s->d_leaf_geom); cudaFree(s->d_leaf_meta);
     cudaFree(s->d_pokeballs); cudaFree(s->d_affines); cudaFree(s->d_ops); cudaFree(s->d_materials);
     cudaFree(s->d_lights); cudaFree(s->d_fallbacks); cudaFree(s->d_runs); cudaFree(s->d_clusters); cudaFree(s->d_obj_orig); cudaFree(s->d_masks);
     delete s;
 }
+}  // namespace
+
+extern "C" {
 
 // Host-only view of the device layout rt_scene_upload would build (no GPU needed): the permutation of the top-level
 // objects, the runs (kind, first, count, 1 + first cluster | 0) and the cluster bounds.  Any output may be NULL.
@@ -405,9 +438,8 @@ int ensure_mt_table(long long tiles) {
         cudaFree(g_ctx.mt_table);
         g_ctx.mt_table = nt; g_ctx.mt_capacity = cap;
     }
-    const char* seq = std::getenv("RT_MT_SEQUENTIAL");            // test hook: the twist-by-twist walk from the resume state
-    if (seq && seq[0] == '1') {
-        if (g_ctx.mt_resume_tiles != g_ctx.mt_tiles) return fail(RT_ERR_STATE, "RT_MT_SEQUENTIAL: the table was built by jumps; call rt_shutdown first");
+    if (g_opts.mt_sequential == 1) {                               // test hook: the twist-by-twist walk from the resume state
+        if (g_ctx.mt_resume_tiles != g_ctx.mt_tiles) return fail(RT_ERR_STATE, "mt_sequential: the table was built by jumps; call rt_shutdown first");
         rtd::mt_checkpoint_kernel<<<1, 640, 0, g_ctx.stream>>>(g_ctx.mt_table, g_ctx.mt_resume, g_ctx.mt_tiles, tiles - g_ctx.mt_tiles, tiles - g_ctx.mt_tiles);
         CU(cudaGetLastError());
         CU(cudaStreamSynchronize(g_ctx.stream));
@@ -424,12 +456,15 @@ int ensure_mt_table(long long tiles) {
             CU(cudaMemcpy(g_ctx.d_jump_poly, mt::kJumpPoly, sizeof(mt::kJumpPoly), cudaMemcpyHostToDevice));
             CU(cudaFuncSetAttribute(rtd::mt_jump_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, rtd::kJumpSmemBytes));
         }
+        int top = 0; while ((1ll << top) < n_seg) ++top;
+        if (top + kSegLog2Twists > mt::kJumpPolys) return fail(RT_ERR_LIMIT, "frame too large for the jump table");
         uint32_t* seg = nullptr;
         CU(cudaMalloc((void**)&seg, (size_t)n_seg * mt::kN * sizeof(uint32_t)));
         uint32_t seed[mt::kN]; mt::seed_state(12345u, seed);                  // tracer.cpp:284
-        CU(cudaMemcpyAsync(seg, seed, sizeof(seed), cudaMemcpyHostToDevice, g_ctx.stream));
-        int top = 0; while ((1ll << top) < n_seg) ++top;
-        if (top + kSegLog2Twists > mt::kJumpPolys) { cudaFree(seg); return fail(RT_ERR_LIMIT, "frame too large for the jump table"); }
+        {
+            cudaError_t e0 = cudaMemcpyAsync(seg, seed, sizeof(seed), cudaMemcpyHostToDevice, g_ctx.stream);
+            if (e0 != cudaSuccess) { cudaFree(seg); return fail(RT_ERR_CUDA, std::string("jitter checkpoint table: ") + cudaGetErrorString(e0)); }
+        }
         for (int l = top - 1; l >= 0; --l) {
             const long long stride = 1ll << l, pairs = (n_seg + 2 * stride - 1) / (2 * stride);
             rtd::mt_jump_kernel<<<(unsigned)pairs, 640, rtd::kJumpSmemBytes, g_ctx.stream>>>(g_ctx.d_jump_poly + (size_t)(l + kSegLog2Twists) * mt::kN, seg, stride, n_seg);
@@ -660,15 +695,18 @@ int rt_trace_rays(rt_scene* s, int n, const double* rays, double* out) {
     cudaStream_t st = g_ctx.stream;
     int rc = bind_scene(s, st); if (rc) return rc;
     double *d_in = nullptr, *d_out = nullptr;
-    CU(cudaMalloc((void**)&d_in, (size_t)n * 6 * sizeof(double)));
-    CU(cudaMalloc((void**)&d_out, (size_t)n * 16 * sizeof(double)));
-    CU(cudaMemcpyAsync(d_in, rays, (size_t)n * 6 * sizeof(double), cudaMemcpyHostToDevice, st));
+    CU(cudaMalloc((void**)&d_in, (size_t)n * 22 * sizeof(double)));          // one allocation: rays in, records out
+    d_out = d_in + (size_t)n * 6;
+    {
+        cudaError_t e0 = cudaMemcpyAsync(d_in, rays, (size_t)n * 6 * sizeof(double), cudaMemcpyHostToDevice, st);
+        if (e0 != cudaSuccess) { cudaFree(d_in); return fail(RT_ERR_CUDA, std::string("rt_trace_rays: ") + cudaGetErrorString(e0)); }
+    }
     if (s->fits_const) rtd::trace_rays_kernel<true><<<(n + 127) / 128, 128, s->smem_bytes, st>>>(d_in, d_out, n);
     else rtd::trace_rays_kernel<false><<<(n + 127) / 128, 128, 0, st>>>(d_in, d_out, n);
     cudaError_t e = cudaGetLastError();
     if (e == cudaSuccess) e = cudaMemcpyAsync(out, d_out, (size_t)n * 16 * sizeof(double), cudaMemcpyDeviceToHost, st);
     if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-    cudaFree(d_in); cudaFree(d_out);
+    cudaFree(d_in);
     if (e != cudaSuccess) return fail(RT_ERR_CUDA, std::string("rt_trace_rays: ") + cudaGetErrorString(e));
     return RT_OK;
 }

@@ -18,7 +18,7 @@ void rt_set_error(const std::string& message) { g_error = message; }
 
 // definition lives in scene_compiler.cpp
 struct rt_compiled;
-namespace rtb { void destroy_compiled(rt_compiled*); const rt_scene_desc* desc_of(const rt_compiled*); }
+namespace rtb { void destroy_compiled(rt_compiled*); const rt_scene_desc* desc_of(const rt_compiled*); void add_dir_light(rt_compiled*, const DirectionalLight&); }
 
 extern "C" {
 
@@ -53,6 +53,14 @@ int rt_compile_json_file(const char* path, rt_compiled** out) {
 
 const rt_scene_desc* rt_compiled_desc(const rt_compiled* c) { return c ? rtb::desc_of(c) : nullptr; }
 void rt_compiled_free(rt_compiled* c) { if (c) rtb::destroy_compiled(c); }
+
+int rt_compiled_add_dir_light(rt_compiled* c, const double dir[3], const double radiance[3]) {
+    if (!c || !dir || !radiance) { rt_set_error("rt_compiled_add_dir_light: null argument"); return RT_ERR_ARG; }
+    rtb::DirectionalLight L;
+    L.dir = {dir[0], dir[1], dir[2]}; L.radiance = {radiance[0], radiance[1], radiance[2]};
+    rtb::add_dir_light(c, L);
+    return RT_OK;
+}
 
 int rt_debug_mt_block_host(uint32_t seed, uint64_t block, uint32_t* out624) {
     if (!out624) { rt_set_error("rt_debug_mt_block_host: null argument"); return RT_ERR_ARG; }

@@ -354,26 +354,33 @@ __device__ __forceinline__ RGBf rgb(float r, float g, float b) { RGBf c; c.r = r
 __device__ __forceinline__ float screen1(float a, float b) { return 1.f - (1.f - a) * (1.f - b); }
 __device__ __forceinline__ RGBf screen(RGBf a, RGBf b) { return rgb(screen1(a.r, b.r), screen1(a.g, b.g), screen1(a.b, b.b)); }
 
+// Direction to light `lp` and its distance (shading.cpp:80-92; a directional light, lp.w != 0, is at infinity: shading.cpp:47).
+__device__ __forceinline__ float light_vector(float4 lp, V3 p, V3 n, V3& wi, float& dist) {
+    if (lp.w != 0.f) { wi = mk(lp.x, lp.y, lp.z); dist = kInf; return fmaxf(0.f, dot(n, wi)); }
+    V3 L = mk(lp.x - p.x, lp.y - p.y, lp.z - p.z);
+    float d2 = fmaxf(dot(L, L), 0.01f);
+    dist = sqrtf(d2);
+    float inv = 1.f / dist;
+    wi = mk(L.x * inv, L.y * inv, L.z * inv);
+    return fmaxf(0.f, dot(n, wi));
+}
 // One light's contribution, screen-blended into E (shading.cpp:79-130).
 template <bool C, bool K>
 __device__ __forceinline__ void light_term(int l, const float4 m0, float ks, float shininess, float kd, V3 n, V3 p, V3 so, V3 wo,
                                            float eps, RGBf& E, Counters& cnt) {
     const float4 lp = SV<C>::light(l, 0), li = SV<C>::light(l, 1);
-    V3 L = mk(lp.x - p.x, lp.y - p.y, lp.z - p.z);
-    float d2 = fmaxf(dot(L, L), 0.01f);
-    float dist = sqrtf(d2);
-    float inv = 1.f / dist;
-    V3 wi = mk(L.x * inv, L.y * inv, L.z * inv);
-    float ndotl = fmaxf(0.f, dot(n, wi));
+    V3 wi; float dist;
+    const float ndotl = light_vector(lp, p, n, wi, dist);
     if (ndotl <= 0.f) return;
     float tmaxS = dist - eps;
     if (tmaxS <= eps) return;
     ++cnt.shadow;
     if (occluded<C, K>(so, normalized(wi), eps, tmaxS, cnt)) return;            // Ray ctor re-normalises (core.h:278)
+    const bool directional = lp.w != 0.f;
     float eff = fmaxf(0.5f, dist);
-    float fall = 2.0f / (eff * eff);                                         // falloff * 2.0 (shading.cpp:108-112)
+    float fall = directional ? 1.f : 2.0f / (eff * eff);                     // falloff * 2.0 (shading.cpp:108-112); none for a directional light
     RGBf I = rgb(li.x * fall, li.y * fall, li.z * fall);
-    float kdn = kd * ndotl * 1.5f;                                           // shading.cpp:115
+    float kdn = directional ? kd * ndotl : kd * ndotl * 1.5f;                // shading.cpp:115 / :61
     RGBf Ed = rgb(m0.x * I.r * kdn, m0.y * I.g * kdn, m0.z * I.b * kdn);
     RGBf Es = rgb(0.f, 0.f, 0.f);
     if (ks > 0.f) {                                                          // shading.cpp:118-126
@@ -389,14 +396,6 @@ __device__ __forceinline__ void light_term(int l, const float4 m0, float ks, flo
 
 // The same term in two halves, for trace_flat: the shadow query first (light_visible), the contribution later (light_shade;
 // the light vector is recomputed, 15 instructions), so that no shading state is live across the scans of a flat scene.
-__device__ __forceinline__ float light_vector(float4 lp, V3 p, V3 n, V3& wi, float& dist) {
-    V3 L = mk(lp.x - p.x, lp.y - p.y, lp.z - p.z);
-    float d2 = fmaxf(dot(L, L), 0.01f);
-    dist = sqrtf(d2);
-    float inv = 1.f / dist;
-    wi = mk(L.x * inv, L.y * inv, L.z * inv);
-    return fmaxf(0.f, dot(n, wi));
-}
 template <bool C, bool K>
 __device__ __forceinline__ bool light_visible(int l, V3 n, V3 p, V3 so, float eps, Counters& cnt) {
     V3 wi; float dist;
@@ -409,13 +408,14 @@ __device__ __forceinline__ bool light_visible(int l, V3 n, V3 p, V3 so, float ep
 }
 template <bool C>
 __device__ __forceinline__ void light_shade(int l, const float4 m0, float ks, float shininess, float kd, V3 n, V3 p, V3 wo, RGBf& E) {
-    const float4 li = SV<C>::light(l, 1);
+    const float4 lp = SV<C>::light(l, 0), li = SV<C>::light(l, 1);
     V3 wi; float dist;
-    const float ndotl = light_vector(SV<C>::light(l, 0), p, n, wi, dist);
+    const float ndotl = light_vector(lp, p, n, wi, dist);
+    const bool directional = lp.w != 0.f;
     float eff = fmaxf(0.5f, dist);
-    float fall = 2.0f / (eff * eff);                                         // falloff * 2.0 (shading.cpp:108-112)
+    float fall = directional ? 1.f : 2.0f / (eff * eff);                     // falloff * 2.0 (shading.cpp:108-112); none for a directional light
     RGBf I = rgb(li.x * fall, li.y * fall, li.z * fall);
-    float kdn = kd * ndotl * 1.5f;                                           // shading.cpp:115
+    float kdn = directional ? kd * ndotl : kd * ndotl * 1.5f;                // shading.cpp:115 / :61
     RGBf Ed = rgb(m0.x * I.r * kdn, m0.y * I.g * kdn, m0.z * I.b * kdn);
     RGBf Es = rgb(0.f, 0.f, 0.f);
     if (ks > 0.f) {                                                          // shading.cpp:118-126

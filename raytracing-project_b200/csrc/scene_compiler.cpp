@@ -361,8 +361,25 @@ public:
 
 struct rt_compiled {
     Compiler c;
+    std::vector<rt_dir_light> dir_lights;
     rt_scene_desc desc{};
 };
+
+namespace {
+// shading.cpp:47: wi = (-light.dir).normalized(); the Ray constructor normalises once more (core.h:278)
+rt_dir_light make_dir_light(const rtb::DirectionalLight& L) {
+    auto unit = [](double& x, double& y, double& z) {
+        const double len = std::sqrt(x * x + y * y + z * z);
+        if (len > 1e-6) { x /= len; y /= len; z /= len; } else { x = 0; y = 1; z = 0; }       // core.h:95-101
+    };
+    double x = -L.dir.x, y = -L.dir.y, z = -L.dir.z;
+    unit(x, y, z); unit(x, y, z);
+    rt_dir_light l{};
+    l.to_light[0] = (float)x; l.to_light[1] = (float)y; l.to_light[2] = (float)z;
+    l.radiance[0] = (float)L.radiance.r; l.radiance[1] = (float)L.radiance.g; l.radiance[2] = (float)L.radiance.b;
+    return l;
+}
+}  // namespace
 
 namespace rtb {
 
@@ -381,7 +398,9 @@ rt_compiled* compile_scene(const Scene& scene, const Camera& cam) {
         l.intensity[0] = (float)L.intensity.r; l.intensity[1] = (float)L.intensity.g; l.intensity[2] = (float)L.intensity.b;
         c.lights.push_back(l);
     }
+    for (const auto& L : scene.dir_lights) out->dir_lights.push_back(make_dir_light(L));
     rt_scene_desc& d = out->desc;
+    d.n_dir_lights = (int)out->dir_lights.size(); d.dir_lights = out->dir_lights.data();
     d.eye[0] = cam.eye.x; d.eye[1] = cam.eye.y; d.eye[2] = cam.eye.z;
     d.screen_p[0] = cam.screen.P.x; d.screen_p[1] = cam.screen.P.y; d.screen_p[2] = cam.screen.P.z;
     d.lx = cam.screen.Lx; d.ly = cam.screen.Ly;
@@ -406,4 +425,8 @@ rt_compiled* compile_scene(const Scene& scene, const Camera& cam) {
 namespace rtb {
 void destroy_compiled(rt_compiled* c) { delete c; }
 const rt_scene_desc* desc_of(const rt_compiled* c) { return &c->desc; }
+void add_dir_light(rt_compiled* c, const DirectionalLight& L) {
+    c->dir_lights.push_back(make_dir_light(L));
+    c->desc.n_dir_lights = (int)c->dir_lights.size(); c->desc.dir_lights = c->dir_lights.data();
+}
 }  // namespace rtb

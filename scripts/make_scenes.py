@@ -184,8 +184,50 @@ def quirks() -> dict:
             "objects": objs}
 
 
+def quirks_far() -> dict:
+    """quirks seen from 36 units away (primary t ~ 35-40: the FP64 epsilons 1e-6 of the CSG comparator and of the
+    secondary-ray offsets are below one FP32 ulp there), plus CSG nodes whose children have COINCIDENT faces:
+    identical spheres under difference / intersection / union, a zero-thickness slab between two half-spaces on one
+    plane, two spheres touching in a point, and a reflective + a refractive sphere far from the eye."""
+    sc = quirks()
+    m = lambda d, **kw: dict({"diffuse": d, "ambient": [0.2, 0.2, 0.2], "specular": [0.3] * 3, "shininess": 20}, **kw)
+    sph = lambda p, r, col, **kw: {"sphere": dict({"position": p, "radius": r, "color": col}, **kw)}
+    hs = lambda p, n, col: {"halfSpace": {"position": p, "normal": n, "color": col}}
+    sc["objects"] += [
+        {"csg": {"operator": "difference", "left": sph([-0.2, 2.1, -2.0], 0.4, m([0.9, 0.2, 0.6])), "right": sph([-0.2, 2.1, -2.0], 0.4, m([0.2, 0.9, 0.6]))}},
+        {"intersection": [sph([-1.3, 2.0, -2.0], 0.4, m([0.9, 0.5, 0.2])), sph([-1.3, 2.0, -2.0], 0.4, m([0.2, 0.5, 0.9]))]},
+        {"union": [sph([0.35, -1.0, 0.2], 0.3, m([0.9, 0.9, 0.9])), sph([0.35, -1.0, 0.2], 0.3, m([0.1, 0.1, 0.1])),
+                   sph([0.95, -1.0, 0.2], 0.3, m([0.6, 0.2, 0.2]))]},                      # the third one touches the pair in one point
+        {"intersection": [sph([-0.6, -1.0, 0.4], 0.35, m([0.3, 0.7, 0.7])), hs([0, -1.0, 0], [0, 1, 0], m([0.7, 0.7, 0.3])),
+                          hs([0, -1.0, 0], [0, -1, 0], m([0.7, 0.3, 0.7]))]},               # slab of zero thickness
+        {"csg": {"operator": "difference", "left": sph([1.5, 1.9, -1.5], 0.45, m([0.8, 0.8, 0.2])),
+                 "right": hs([0, 1.9, 0], [0, 1, 0], m([0.2, 0.2, 0.8]))}},                  # cut through the centre: coplanar with nothing, control
+        sph([-2.6, -0.6, -3.0], 0.5, m([0.7, 0.7, 0.75], reflected=[0.6] * 3)),
+        sph([1.9, 0.55, -3.2], 0.5, m([0.1, 0.1, 0.1], refracted=[0.85] * 3, reflected=[0.1] * 3), index=1.5),
+    ]
+    sc["screen"] = {"dpi": 80, "dimensions": [4, 3], "position": [-2, -1.2, 1], "observer": [0, 0.3, 37]}
+    return sc
+
+
+def big_floor() -> dict:
+    """One huge sphere (the common r = 1000 'floor') plus many small ones: the candidate scan's rounding margin must stay
+    per primitive (a global max(|c|^2 + r^2) would make every small sphere a candidate of every ray)."""
+    rng = np.random.default_rng(20261105)
+    m = lambda d, **kw: dict({"diffuse": d, "ambient": [0.15] * 3, "specular": [0.3] * 3, "shininess": 16}, **kw)
+    objs = [{"sphere": {"position": [0, -1001.0, -4], "radius": 1000.0, "color": m([0.5, 0.55, 0.5])}}]
+    for _ in range(40):
+        p = [float(rng.uniform(-3, 3)), float(rng.uniform(-0.8, 1.6)), float(rng.uniform(-7, -1.5))]
+        objs.append({"sphere": {"position": p, "radius": float(rng.uniform(0.12, 0.4)), "color": m([float(v) for v in rng.uniform(0.2, 0.9, 3)])}})
+    return {"screen": {"dpi": 60, "dimensions": [4, 3], "position": [-2, -1.5, 0], "observer": [0, 0.2, 5]},
+            "medium": {"ambient": [0.3, 0.3, 0.3], "index": 1.0, "recursion": 2}, "background": [0.2, 0.3, 0.5],
+            "sources": [{"position": [4, 6, 5], "intensity": [40, 40, 40]}, {"position": [-4, 3, 2], "intensity": [15, 15, 18]}],
+            "objects": objs}
+
+
 def main() -> None:
     examples()
+    dump("quirks_far.json", quirks_far())
+    dump("big_floor.json", big_floor())
     dump("synthetic_a_8k.json", synthetic_a(1440))          # 7680x4320, recursion 8
     dump("synthetic_a_small.json", synthetic_a(60))          # 320x180, same scene: full-frame CPU parity
     dump("synthetic_a_2k.json", synthetic_a(360))           # 1920x1080, same scene: profiling size

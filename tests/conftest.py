@@ -39,6 +39,14 @@ def gpu(rt):
     return rt
 
 
+@pytest.fixture
+def force(gpu):
+    """force(name, value): rt_debug_set_option for this test only (all hooks return to the library default afterwards)."""
+    yield gpu.debug_option
+    for name in gpu.DEBUG_OPTIONS:
+        gpu.debug_option(name, -1)
+
+
 def golden_names():
     return sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN, "*.npz")))
 
@@ -61,3 +69,18 @@ def image_parity(rgb8_a: np.ndarray, rgb8_b: np.ndarray):
     """Fraction of pixels whose channels all agree within 1/255, and the largest channel difference."""
     d = np.abs(rgb8_a.astype(int) - rgb8_b.astype(int)).max(axis=2)
     return float((d <= 1).mean()), int(d.max())
+
+
+def golden_oracle(oa, g):
+    """The oracle's scene for a golden fixture (JSON + the DirectionalLights the fixture was rendered with, if any)."""
+    o = oa.Oracle(g["scene_json"])
+    for row in g.get("dir_lights", []):
+        o.add_dir_light(row[:3], row[3:])
+    return o
+
+
+def golden_gpu_scene(gpu, g):
+    sc = gpu.load_scene_from_json_text(g["scene_json"])
+    for row in g.get("dir_lights", []):
+        sc.add_dir_light(row[:3], row[3:])
+    return sc

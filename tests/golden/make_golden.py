@@ -16,7 +16,10 @@ CASES = {  # fixture name -> (scene file, dpi)
     "quirks": ("quirks.json", 24), "pokeballs": ("pokeballs.json", 24), "penguin": ("penguin.json", 24),
     "snorlax_reflect": ("snorlax_4k_reflect.json", 18), "synthetic_a": ("synthetic_a_tiny.json", 18),
     "synthetic_b": ("synthetic_b_small.json", 16),
+    # the same quirks scene lit by two DirectionalLights as well (scene.h:10-19; pushed into scene.dir_lights by ref_driver --dirlight)
+    "quirks_dirlight": ("quirks.json", 24),
 }
+DIR_LIGHTS = {"quirks_dirlight": [((-0.3, -1.0, -0.5), (0.8, 0.7, 0.6)), ((0.5, -0.2, -1.0), (0.3, 0.3, 0.5))]}
 
 def rays_for(scene: dict, n: int, seed: int) -> np.ndarray:
     """Camera-ish rays plus rays started near/inside the objects' region (exercise secondary-ray quirks)."""
@@ -34,18 +37,23 @@ def rays_for(scene: dict, n: int, seed: int) -> np.ndarray:
 
 def main():
     assert oa.have_ref(), "oracle/_ref/ref_driver missing: run `make -C oracle ref` where /root/reference exists"
+    only = sys.argv[1:]
     for name, (fname, dpi) in CASES.items():
+        if only and name not in only:
+            continue
         scene = json.load(open(os.path.join(ROOT, "scenes", fname)))
         scene["screen"]["dpi"] = dpi
         text = json.dumps(scene, separators=(",", ":"))
         with tempfile.NamedTemporaryFile("w", suffix=".json", delete=False) as f:
             f.write(text); path = f.name
-        std = oa.ref_render(path, "standard", want_ids=True)
-        pap = oa.ref_render(path, "paper", want_ids=True)
+        dl = DIR_LIGHTS.get(name, [])
+        std = oa.ref_render(path, "standard", want_ids=True, dir_lights=dl)
+        pap = oa.ref_render(path, "paper", want_ids=True, dir_lights=dl)
         rays = rays_for(scene, 768, 1234 + len(name))
-        rec = oa.ref_trace_rays(path, rays)
+        rec = oa.ref_trace_rays(path, rays, dir_lights=dl)
         os.unlink(path)
-        np.savez_compressed(os.path.join(HERE, name + ".npz"), scene_json=np.array(text),
+        extra = {"dir_lights": np.array([list(d) + list(r) for d, r in dl], float)} if dl else {}
+        np.savez_compressed(os.path.join(HERE, name + ".npz"), scene_json=np.array(text), **extra,
                             std_fb=std["fb"], std_ids=std["ids"], std_t=std["t"],
                             paper_fb=pap["fb"], paper_ids=pap["ids"], paper_t=pap["t"], rays=rays, ray_records=rec)
         print(name, std["fb"].shape, os.path.getsize(os.path.join(HERE, name + ".npz")) // 1024, "KiB")

@@ -40,6 +40,7 @@ def lib():
         L.orc_scene_load.restype = C.c_void_p
         L.orc_scene_load.argtypes = [C.c_char_p, C.c_char_p, C.c_int]
         L.orc_scene_free.argtypes = [C.c_void_p]
+        L.orc_add_dir_light.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_scene_info.argtypes = [C.c_void_p, C.POINTER(C.c_int)]
         L.orc_render.restype = C.c_int
         L.orc_render.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
@@ -70,6 +71,11 @@ class Oracle:
     def from_file(cls, path: str) -> "Oracle":
         with open(path) as f:
             return cls(f.read())
+
+    def add_dir_light(self, direction, radiance):
+        """scene.dir_lights.push_back({dir, radiance}) (scene.h:10-19,37)."""
+        d = np.asarray(direction, np.float64); r = np.asarray(radiance, np.float64)
+        lib().orc_add_dir_light(self._h, d.ctypes.data_as(C.c_void_p), r.ctypes.data_as(C.c_void_p))
 
     def close(self):
         if self._h:
@@ -152,10 +158,13 @@ def _read_ids(path):
         return ids, ts
 
 
-def ref_render(scene_path: str, mode: str = "standard", rows=None, want_ids=False, timeout=3600):
-    """Run the reference build on a scene file; returns dict(fb, ids, t, render_ms)."""
+def ref_render(scene_path: str, mode: str = "standard", rows=None, want_ids=False, timeout=3600, dir_lights=()):
+    """Run the reference build on a scene file; returns dict(fb, ids, t, render_ms).
+    dir_lights: [(direction xyz, radiance rgb)] pushed into scene.dir_lights (the JSON format has none)."""
     with tempfile.TemporaryDirectory() as td:
         cmd = [REF_DRIVER, scene_path, "--quiet", "--fb", os.path.join(td, "o.fb")]
+        for d, r in dir_lights:
+            cmd += ["--dirlight"] + [repr(float(v)) for v in list(d) + list(r)]
         if mode == "paper":
             cmd.append("--paper")
         if rows is not None:
@@ -170,14 +179,17 @@ def ref_render(scene_path: str, mode: str = "standard", rows=None, want_ids=Fals
         return out
 
 
-def ref_trace_rays(scene_path: str, rays: np.ndarray) -> np.ndarray:
+def ref_trace_rays(scene_path: str, rays: np.ndarray, dir_lights=()) -> np.ndarray:
     rays = np.ascontiguousarray(rays, np.float64).reshape(-1, 6)
     with tempfile.TemporaryDirectory() as td:
         fi, fo = os.path.join(td, "in.rays"), os.path.join(td, "out.rays")
         with open(fi, "wb") as f:
             f.write(np.int32(rays.shape[0]).tobytes())
             f.write(rays.tobytes())
-        subprocess.run([REF_DRIVER, scene_path, "--quiet", "--rays", fi, fo], check=True, capture_output=True)
+        extra = []
+        for d, r in dir_lights:
+            extra += ["--dirlight"] + [repr(float(v)) for v in list(d) + list(r)]
+        subprocess.run([REF_DRIVER, scene_path, "--quiet", "--rays", fi, fo] + extra, check=True, capture_output=True)
         with open(fo, "rb") as f:
             n = int(np.frombuffer(f.read(4), np.int32)[0])
             return np.frombuffer(f.read(), np.float64).reshape(n, 16).copy()

@@ -11,7 +11,7 @@ import subprocess
 import numpy as np
 import pytest
 
-from conftest import golden_names, image_parity, scene_path
+from conftest import golden_gpu_scene, golden_names, image_parity, scene_path
 
 pytestmark = pytest.mark.gpu
 
@@ -28,7 +28,9 @@ def render_gpu(gpu, scene, mode, **kw):
 def assert_parity(got, want_fb, want_ids, oa, label):
     frac, worst = image_parity(got["rgb8"], oa.to_byte(want_fb))
     bad = float((got["ids"] != want_ids).mean())
-    print(f"{label}: px within 1/255 = {frac:.6f} (max diff {worst}), id mismatches = {int((got['ids'] != want_ids).sum())} ({bad:.2e})")
+    n_px = int((np.abs(got["rgb8"].astype(int) - oa.to_byte(want_fb).astype(int)).max(axis=2) > 1).sum())
+    print(f"{label}: px within 1/255 = {frac:.6f} ({n_px} of {got['rgb8'].shape[0] * got['rgb8'].shape[1]} pixels off, max diff {worst}), "
+          f"silhouette samples with another id = {int((got['ids'] != want_ids).sum())} of {want_ids.size} ({bad:.2e})")
     assert bad <= ID_TOL, f"{label}: id mismatch fraction {bad}"
     assert frac >= PX_TOL, f"{label}: only {frac} of the pixels within 1/255"
     # the float framebuffer and the 8-bit image are the same data
@@ -36,7 +38,10 @@ def assert_parity(got, want_fb, want_ids, oa, label):
 
 
 SMALL = ["quirks", "pokeballs_small", "penguin_small", "snorlax_small", "snorlax_4k_small", "snorlax_4k_reflect_small",
-         "synthetic_a_tiny", "synthetic_b_small"]
+         "synthetic_a_tiny", "synthetic_b_small",
+         "synthetic_a_small",      # BASELINE configs[3]'s own scene (1 000 spheres + 64 pokeballs + 32 wrapped CSG, recursion 8), whole frame
+         "quirks_far",             # t ~ 36: FP64 epsilons below one FP32 ulp, coincident CSG faces
+         "big_floor"]              # one r = 1000 sphere + 40 small ones (per-primitive mask margin)
 
 
 @pytest.mark.parametrize("mode", ["standard", "paper"])
@@ -53,25 +58,31 @@ def test_scene_matches_oracle(gpu, oa, name, mode):
 def test_scene_matches_reference_fixture(gpu, oa, goldens, name, mode):
     """Against the committed outputs of the unmodified reference build (tests/golden)."""
     g = goldens[name]
-    got, _ = render_gpu(gpu, gpu.load_scene_from_json_text(g["scene_json"]), mode)
+    got, _ = render_gpu(gpu, golden_gpu_scene(gpu, g), mode)
     key = "std" if mode == "standard" else "paper"
     frac, worst = image_parity(got["rgb8"], oa.to_byte(g[key + "_fb"]))
     bad = float((got["ids"] != g[key + "_ids"]).mean())
     print(f"golden {name}/{mode}: px {frac:.5f} max {worst} ids {bad:.2e}")
-    assert bad <= 2e-3 and frac >= 0.998      # ~6k-pixel images: one silhouette pixel is 1.6e-4
+    n_bad = int((got["ids"] != g[key + "_ids"]).sum())
+    print(f"golden {name}/{mode}: {n_bad} of {g[key + '_ids'].size} samples with another id")
+    assert bad <= ID_TOL and frac >= PX_TOL   # north_star's bounds; a ~6k-pixel image has ~55k samples
 
 
 @pytest.mark.parametrize("name", golden_names())
 def test_rays_match_reference_fixture(gpu, goldens, name):
     """Arbitrary rays (half start inside the scene volume: secondary-ray quirks of SURVEY.md §3.4)."""
     g = goldens[name]
-    rec = gpu.Tracer(gpu.load_scene_from_json_text(g["scene_json"])).trace_rays(g["rays"])
+    rec = gpu.Tracer(golden_gpu_scene(gpu, g)).trace_rays(g["rays"])
     ref = g["ray_records"]
     same_hit = rec[:, 0] == ref[:, 0]
-    assert same_hit.mean() >= 0.995, f"hit/miss agreement {same_hit.mean()}"
     both = same_hit & (ref[:, 0] == 1)
     same_obj = rec[both, 9] == ref[both, 9]
-    assert same_obj.mean() >= 0.99
+    print(f"golden rays {name}: {int((~same_hit).sum())} of {len(ref)} rays disagree on hit/miss, {int((~same_obj).sum())} of {int(both.sum())} on the object; "
+          f"front_face {int((rec[both, 8] != ref[both, 8]).sum())}, occlusion probe {int((rec[:, 13] != ref[:, 13]).sum())}")
+    # random rays graze silhouettes like camera rays do: the counted set is bounded at 2 rays of 768 (north_star's 1e-3 of
+    # samples is less than one ray here)
+    assert (~same_hit).sum() <= 2, f"hit/miss agreement {same_hit.mean()}"
+    assert (~same_obj).sum() <= 2
     ok = both.copy(); ok[both] = same_obj
     assert np.allclose(rec[ok, 1], ref[ok, 1], rtol=2e-4, atol=2e-4), "hit distance"
     # normals compared where the reference's is non-degenerate (it records zero normals for origin-inside CSG entries)
@@ -83,22 +94,24 @@ def test_rays_match_reference_fixture(gpu, goldens, name):
 
 
 def test_jitter_stream_is_bit_exact(gpu, oa):
-    for first, n in [(0, 5000), (1247, 3), (1248, 1248 * 3), (8 * 3840 * 1000 + 5, 4000), (2_000_000_000, 2500)]:
+    # the last entries straddle sample 2^31 - 1, the last sample of a 16384 x 16384 frame (BASELINE configs[4]); the
+    # oracle has to discard 8.6 G generator outputs to get there (~40 s)
+    for first, n in [(0, 5000), (1247, 3), (1248, 1248 * 3), (8 * 3840 * 1000 + 5, 4000), (2_000_000_000, 2500),
+                     ((1 << 31) - 2500, 2500 + 300)]:
         assert np.array_equal(gpu.debug_jitter(first, n), oa.jitter(first, n)), (first, n)
 
 
-def test_checkpoint_table_by_jumps_equals_the_sequential_walk(gpu, oa, monkeypatch):
-    """The checkpoint table is built by GF(2) jump-ahead (segment start states) + short parallel walks; RT_MT_SEQUENTIAL=1
-    forces the twist-by-twist walk from the seed.  Both must give the same stream, also when the table grows."""
+def test_checkpoint_table_by_jumps_equals_the_sequential_walk(gpu, oa, force):
+    """The checkpoint table is built by GF(2) jump-ahead (segment start states) + short parallel walks; the mt_sequential
+    hook forces the twist-by-twist walk from the seed.  Both must give the same stream, also when the table grows."""
     probes = [(0, 3000), (64 * 1248 - 7, 40), (1248 * 777 + 3, 2500), (40_000_000, 1500)]
     out = {}
-    for force in ("1", "0"):
+    for seq in (1, 0):
         gpu.shutdown()
-        monkeypatch.setenv("RT_MT_SEQUENTIAL", force)
+        force("mt_sequential", seq)
         gpu.init(0)
-        out[force] = [gpu.debug_jitter(first, n) for first, n in probes]          # the table grows from probe to probe
-    monkeypatch.delenv("RT_MT_SEQUENTIAL")
-    for (first, n), a, b in zip(probes, out["1"], out["0"]):
+        out[seq] = [gpu.debug_jitter(first, n) for first, n in probes]          # the table grows from probe to probe
+    for (first, n), a, b in zip(probes, out[1], out[0]):
         assert np.array_equal(a, b), (first, n)
         assert np.array_equal(b, oa.jitter(first, n)), (first, n)
 
@@ -139,15 +152,15 @@ def test_render_is_deterministic_and_device_path_matches(gpu):
 
 
 @pytest.mark.parametrize("name", ["quirks", "synthetic_b_small", "snorlax_4k_reflect_small", "pokeballs_small"])
-def test_wavefront_and_per_thread_kernels_agree(gpu, name, monkeypatch):
+def test_wavefront_and_per_thread_kernels_agree(gpu, name, force):
     """Scenes with deep ray trees run the CTA-wavefront kernel, the others one sample per thread; forced either way
-    (RT_FORCE_WAVEFRONT is read at upload) the two must produce the same frame bit for bit, ids included."""
+    (the hook is read at upload) the two must produce the same frame bit for bit, ids included."""
     out = {}
-    for force in ("0", "1"):
-        monkeypatch.setenv("RT_FORCE_WAVEFRONT", force)
+    for w in ("0", "1"):
+        force("wavefront", int(w))
         sc = gpu.load_scene_from_json(scene_path(name))
-        out[force], tr = render_gpu(gpu, sc, "standard")
-        out[force + "stats"] = tr.last_stats
+        out[w], tr = render_gpu(gpu, sc, "standard")
+        out[w + "stats"] = tr.last_stats
         sc.close()
     for k in ("rgb8", "fb", "ids"):
         assert np.array_equal(out["0"][k], out["1"][k]), k
@@ -156,16 +169,16 @@ def test_wavefront_and_per_thread_kernels_agree(gpu, name, monkeypatch):
 
 
 @pytest.mark.parametrize("name", ["snorlax_small", "pokeballs_small", "penguin_small", "synthetic_a_tiny"])
-def test_flat_kernel_and_generic_loop_agree(gpu, name, monkeypatch):
+def test_flat_kernel_and_generic_loop_agree(gpu, name, force):
     """A scene in which no ray can spawn a child runs trace_flat (one closest hit + one shade, optionally with the CTA in
-    lockstep per light); forced back onto the generic stack loop (RT_FORCE_FLAT=0) or in / out of lockstep
-    (RT_FORCE_LOCKSTEP), frame, ids and ray counts must not change by a bit."""
+    lockstep per light); forced back onto the generic stack loop (flat = 0) or in / out of lockstep, frame, ids and ray
+    counts must not change by a bit."""
     out = []
-    for env in ({"RT_FORCE_FLAT": "0"}, {"RT_FORCE_LOCKSTEP": "0"}, {"RT_FORCE_LOCKSTEP": "1"}):
-        for k in ("RT_FORCE_FLAT", "RT_FORCE_LOCKSTEP"):
-            monkeypatch.delenv(k, raising=False)
+    for env in ({"flat": 0}, {"lockstep": 0}, {"lockstep": 1}):
+        for k in ("flat", "lockstep"):
+            force(k, -1)
         for k, v in env.items():
-            monkeypatch.setenv(k, v)
+            force(k, v)
         sc = gpu.load_scene_from_json(scene_path(name))
         got, tr = render_gpu(gpu, sc, "standard")
         out.append((got, dict(tr.last_stats)))
@@ -177,11 +190,11 @@ def test_flat_kernel_and_generic_loop_agree(gpu, name, monkeypatch):
             assert out[0][1][k] == st[k], k
 
 
-def test_every_scene_data_path_agrees(gpu, monkeypatch):
-    """RT_FORCE_GLOBAL: the scene read through the global read-only path instead of the staged shared-memory image."""
+def test_every_scene_data_path_agrees(gpu, force):
+    """global_scene hook: the scene read through the global read-only path instead of the staged shared-memory image."""
     ref = None
-    for force in ("0", "1"):
-        monkeypatch.setenv("RT_FORCE_GLOBAL", force)
+    for g in (0, 1):
+        force("global_scene", g)
         sc = gpu.load_scene_from_json(scene_path("synthetic_a_tiny"))
         got, _ = render_gpu(gpu, sc, "standard")
         sc.close()
@@ -252,6 +265,97 @@ def test_full_resolution_bands_match_oracle(gpu, oa, name, bands):
         rows = slice(H - y1, H - y0)
         sub = {k: got[k][rows] for k in ("rgb8", "fb", "ids")}
         assert_parity(sub, want["fb"][rows], want["ids"][rows], oa, f"{name} rows {y0}-{y1}")
+
+
+def render_gpu_bands(gpu, path, bands, mode="standard"):
+    """Whole frame on the device (frame, float framebuffer and ids stay there: 13 GB at 16384^2), only the rows of `bands`
+    (LOOP order, tracer.cpp:288: y = 0 is the bottom row) come back.  Returns (scene, [dict(rgb8, fb, ids) per band])."""
+    import torch
+    sc = gpu.load_scene_from_json(path)
+    W, H = sc.width, sc.height
+    tr = gpu.Tracer(sc, gpu.RenderMode(MODES[mode]))
+    S = 8 if mode == "standard" else 1
+    frame = torch.zeros((H, W, 4), dtype=torch.uint8, device="cuda")
+    fbuf = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
+    ids = torch.full((H, W, S), -1, dtype=torch.int32, device="cuda")
+    st = tr.render_device(frame.data_ptr(), fbuf.data_ptr(), ids.data_ptr(), stream=torch.cuda.current_stream().cuda_stream, want_stats=True)
+    torch.cuda.synchronize()
+    assert st["primary_rays"] == W * H * S
+    out = []
+    for y0, y1 in bands:
+        rows = slice(H - y1, H - y0) if mode == "standard" else slice(y0, y1)
+        out.append({"rgb8": frame[rows, :, :3].cpu().numpy(), "fb": fbuf[rows, :, :3].cpu().numpy(), "ids": ids[rows].cpu().numpy(), "rows": rows})
+    del frame, fbuf, ids
+    torch.cuda.empty_cache()
+    return sc, out
+
+
+def check_bands(gpu, oa, name, bands, mode="standard"):
+    p = scene_path(name)
+    sc, got = render_gpu_bands(gpu, p, bands, mode)
+    o = oa.Oracle.from_file(p)
+    for (y0, y1), sub in zip(bands, got):
+        want = o.render(mode, rows=(y0, y1), want_ids=True)
+        assert_parity(sub, want["fb"][sub["rows"]], want["ids"][sub["rows"]], oa, f"{name} rows {y0}-{y1}")
+    sc.close()
+
+
+def test_synthetic_a_8k_bands_match_oracle(gpu, oa):
+    """BASELINE configs[3] at its own size, 7680x4320 recursion 8 (clustered sphere run, clustered pokeball run, 32 wrapped CSG
+    programs with world bounds, non-uniform scalings): rows through the floor, the dense sphere field, the CSG row and the top."""
+    check_bands(gpu, oa, "synthetic_a_8k", [(0, 1), (700, 702), (1800, 1802), (2600, 2602), (4319, 4320)])
+
+
+def test_synthetic_b_4k_bands_match_oracle(gpu, oa):
+    check_bands(gpu, oa, "synthetic_b_4k", [(0, 1), (1500, 1502), (2047, 2049), (4095, 4096)])
+
+
+def test_synthetic_b_16k_last_rows_match_oracle(gpu, oa):
+    """BASELINE configs[4] at 16384x16384: the last rows end at sample 2^31 - 1 of the jitter stream (top levels of the jump
+    table, 64-bit pixel arithmetic).  The oracle discards 8.6 G generator outputs to get there (~1 min)."""
+    check_bands(gpu, oa, "synthetic_b_16k", [(0, 1), (16382, 16384)])
+
+
+@pytest.mark.parametrize("name,mode", [("pokeballs", "standard"), ("penguin", "standard"), ("penguin", "paper"), ("snorlax", "standard")])
+def test_native_size_frames_match_oracle(gpu, oa, name, mode):
+    """BASELINE configs[0] / configs[1] at the reference's native resolutions (1024x768, 1200x900), whole frame."""
+    p = scene_path(name)
+    got, _ = render_gpu(gpu, gpu.load_scene_from_json(p), mode)
+    want = oa.Oracle.from_file(p).render(mode, want_ids=True)
+    assert_parity(got, want["fb"], want["ids"], oa, f"{name} native/{mode}")
+
+
+@pytest.mark.parametrize("recursion", [0, 1, 2])
+@pytest.mark.parametrize("name", ["quirks", "synthetic_b_small"])
+def test_shallow_recursion_limits(gpu, oa, name, recursion):
+    """medium.recursion 0 renders black with the id buffer still defined (tracer.cpp:26), 1 is direct light only."""
+    scene = json.load(open(scene_path(name)))
+    scene["medium"]["recursion"] = recursion
+    text = json.dumps(scene)
+    got, tr = render_gpu(gpu, gpu.load_scene_from_json_text(text), "standard")
+    want = oa.Oracle(text).render("standard", want_ids=True)
+    assert_parity(got, want["fb"], want["ids"], oa, f"{name} recursion {recursion}")
+    if recursion == 0:
+        assert not got["rgb8"].any() and (got["ids"] >= 0).any()
+    if recursion <= 1:
+        assert tr.last_stats["secondary_rays"] == 0
+
+
+def test_directional_lights(gpu, oa):
+    """DirectionalLight (scene.h:10-19, shading.cpp:46-76) through rt_compiled_add_dir_light, both modes, against the oracle
+    (which is pinned to the reference for this by tests/golden/quirks_dirlight.npz and the live ref_driver --dirlight test)."""
+    p = scene_path("snorlax_4k_reflect_small")
+    dl = [((0.3, -1.0, -0.6), (0.7, 0.65, 0.6)), ((-0.8, -0.3, -1.0), (0.25, 0.25, 0.4))]
+    for mode in ("standard", "paper"):
+        sc = gpu.load_scene_from_json(p); o = oa.Oracle.from_file(p)
+        for d, r in dl:
+            sc.add_dir_light(d, r); o.add_dir_light(d, r)
+        got, tr = render_gpu(gpu, sc, mode)
+        want = o.render(mode, want_ids=True)
+        assert_parity(got, want["fb"], want["ids"], oa, f"directional lights/{mode}")
+        plain, tr0 = render_gpu(gpu, gpu.load_scene_from_json(p), mode)
+        assert tr.last_stats["shadow_rays"] > tr0.last_stats["shadow_rays"]
+        assert not np.array_equal(plain["rgb8"], got["rgb8"])
 
 
 def test_paper_4k_matches_oracle_band(gpu, oa):
