@@ -15,6 +15,7 @@
 #include <stdint.h>
 
 #include "../../include/rt_b200.h"
+#include "rt_cull.cuh"
 
 namespace rtd {
 
@@ -25,7 +26,7 @@ struct SceneHeader {
     int recursion, n_objects, n_lights, n_runs, n_leaves, n_ops, n_clusters;
     // shared-memory image (units of 16 B from the start of dynamic shared memory; ops in bytes)
     int off_leaf_geom, off_leaf_meta, off_runs, off_lights, off_clusters, off_masks, off_ops_bytes, smem_bytes;
-    float mask_scale;           // max |c|^2 + r^2 over the finite entries of `masks` (rounding margin of sphere_mask)
+    float mask_scale;           // unused by the device since the margin moved into the table (kept for rt_debug_mask_table)
     const float4* obj_geom; const int4* obj_meta;
     const float4* leaf_geom; const int4* leaf_meta;
     const float4* pokeballs;    // 3 float4 each
@@ -37,7 +38,7 @@ struct SceneHeader {
     const int4* runs;           // kind, first, count, 1 + first cluster (0: run is not clustered)
     const float4* clusters;     // bounding sphere of every 16 consecutive primitives of a clustered run
     const int* obj_orig;        // JSON index of device object i (clustered runs are reordered spatially)
-    const float4* masks;        // (c.xyz, |c|^2 - r^2) of every entry of obj_geom, leaf_geom, clusters (in that order)
+    const float4* masks;        // (c.xyz, |c|^2 - r^2 - 2^-16 (|c|^2 + r^2)) of every entry of obj_geom, leaf_geom, clusters (in that order)
 };
 
 enum { RUN_SPHERE = 0, RUN_HALFSPACE = 1, RUN_POKEBALL = 2, RUN_GENERIC = 3 };
@@ -72,6 +73,10 @@ template <bool C> struct SV {
     static __device__ __forceinline__ float4 fallback(int i)  { return __ldg(c_hdr.fallbacks + i); }
     static __device__ __forceinline__ float4 cluster(int i)   { return C ? reinterpret_cast<const float4*>(s_scene)[c_hdr.off_clusters + i] : __ldg(c_hdr.clusters + i); }
     static __device__ __forceinline__ int    obj_orig(int i)  { return __ldg(c_hdr.obj_orig + i); }
+    // base pointers for cull(): the (centre, radius) entries themselves; G says whether they are in shared memory
+    static __device__ __forceinline__ const float4* leaf_geom_ptr(int i)    { return C ? reinterpret_cast<const float4*>(s_scene) + c_hdr.off_leaf_geom + i : c_hdr.leaf_geom + i; }
+    static __device__ __forceinline__ const float4* cluster_geom_ptr(int i) { return C ? reinterpret_cast<const float4*>(s_scene) + c_hdr.off_clusters + i : c_hdr.clusters + i; }
+    template <bool K> static __device__ __forceinline__ const float4* obj_geom_ptr(int i) { return (C && !K) ? reinterpret_cast<const float4*>(s_scene) + i : c_hdr.obj_geom + i; }
     // base pointers for sphere_mask (the mask table mirrors obj_geom | leaf_geom | clusters)
     static __device__ __forceinline__ const float4* mask_ptr(int i)    { return C ? reinterpret_cast<const float4*>(s_scene) + c_hdr.off_masks + i : c_hdr.masks + i; }
 #if RT_MASK_EXACT
@@ -106,6 +111,23 @@ template <bool C> __device__ __forceinline__ void stage_scene() {
 // materials are indexed per lane (divergent) -> always the global read-only path
 __device__ __forceinline__ float4 material(int m, int k) { return __ldg(c_hdr.materials + m * 3 + k); }
 
+constexpr float kInf = __builtin_huge_valf();
+// ---- warp-level helpers --------------------------------------------------------------------------
+constexpr unsigned kFullWarp = 0xffffffffu;
+// max over the warp into a uniform register (CREDUX); a NaN in any lane gives NaN, which every user treats as "do not cull"
+__device__ __forceinline__ float warp_max_nan(float v) {
+    float r; asm volatile("redux.sync.max.NaN.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v)); return r;
+}
+__device__ __forceinline__ float warp_max(float v) {
+    float r; asm volatile("redux.sync.max.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v)); return r;
+}
+// One bundle record per warp (rt_cull.cuh), written by lane 0 of make_bundle and read by the culls of that query only.
+constexpr int kMaxWarpsPerCta = 8;
+__device__ __forceinline__ Bundle& warp_bundle() {
+    __shared__ __align__(16) Bundle s_bundle[kMaxWarpsPerCta];
+    return s_bundle[threadIdx.x >> 5];
+}
+
 // ---- small vector helpers ---------------------------------------------------------------------
 struct V3 { float x, y, z; };
 __device__ __forceinline__ V3 mk(float x, float y, float z) { V3 v; v.x = x; v.y = y; v.z = z; return v; }
@@ -123,7 +145,6 @@ __device__ __forceinline__ V3 normalized(V3 a) {
     return mk(0.f, 1.f, 0.f);
 }
 
-constexpr float kInf = __builtin_huge_valf();
 }  // namespace rtd
 #include "rt_csg.cuh"
 namespace rtd {
@@ -134,6 +155,52 @@ struct Hit {
 
 // per-thread ray statistics (rt_stats)
 struct Counters { unsigned primary, shadow, secondary, tests; };
+
+// ---- ray bundles (rt_cull.cuh) -----------------------------------------------------------------------
+// Must be called by all 32 lanes of a converged warp; `active` lanes contribute their ray and the far end of their query
+// window.  The central ray is lane 16's when it is active (the middle of the 4 pixels / 32 pixels a warp covers), else the
+// first active lane's.  Returns false when no lane is active.
+__device__ __forceinline__ bool make_bundle(bool active, V3 o, V3 d, float tmax) {
+    const unsigned ballot = __ballot_sync(kFullWarp, active);
+    if (ballot == 0u) return false;
+    const int leader = ((ballot >> 16) & 1u) ? 16 : (__ffs(ballot) - 1);
+    const float mx = __shfl_sync(kFullWarp, o.x, leader), my = __shfl_sync(kFullWarp, o.y, leader), mz = __shfl_sync(kFullWarp, o.z, leader);
+    const float cx = __shfl_sync(kFullWarp, d.x, leader), cy = __shfl_sync(kFullWarp, d.y, leader), cz = __shfl_sync(kFullWarp, d.z, leader);
+    float h2 = 0.f, d2 = 0.f, th = -kInf;
+    if (active) {
+        const float ax = o.x - mx, ay = o.y - my, az = o.z - mz, bx = d.x - cx, by = d.y - cy, bz = d.z - cz;
+        h2 = fmaf(ax, ax, fmaf(ay, ay, az * az));
+        d2 = fmaf(bx, bx, fmaf(by, by, bz * bz));
+        th = tmax;
+    }
+    h2 = warp_max_nan(h2); d2 = warp_max_nan(d2); th = warp_max_nan(th);
+    Bundle& B = warp_bundle();
+    __syncwarp();                                   // the previous query's culls have all read the record
+    if ((threadIdx.x & 31) == 0) {
+        B.mx = mx; B.my = my; B.mz = mz; B.cx = cx; B.cy = cy; B.cz = cz;
+        bundle_finish(B, h2, d2, th);
+        B.any = 1;
+    }
+    __syncwarp();
+    return true;
+}
+
+// Candidate bits of the <= 32 consecutive sphere-like entries p[0..n): lane k tests entry k against the warp's bundle.
+// G: the entries are in shared memory (else the global read-only path).  All lanes of a converged warp must call.
+template <bool G> __device__ __forceinline__ uint32_t cull(const float4* p, int n, float t_hi, bool segment, unsigned& tests) {
+    const Bundle& B = warp_bundle();
+    const uint32_t all = n >= 32 ? 0xffffffffu : ((1u << n) - 1u);
+    if (B.wide) return all;
+    const int lane = threadIdx.x & 31;
+    bool cand = false;
+    if (lane < n) {
+        const float4 g = G ? p[lane] : __ldg(p + lane);
+        Sphere4 q; q.x = g.x; q.y = g.y; q.z = g.z; q.w = g.w;
+        cand = !bundle_rejects(B, q, t_hi, segment);
+        ++tests;
+    }
+    return __ballot_sync(kFullWarp, cand);
+}
 
 // ---- primitive tests -----------------------------------------------------------------------------
 // Quadratic of Sphere::intersect (geometry.cpp:15-22) for a unit direction.  The reference evaluates
@@ -182,7 +249,8 @@ __device__ __forceinline__ bool plane_t(float4 g, V3 o, V3 d, float tmin, float 
 // independent chains in flight.  The form cancels (rounding error ~ 2^-24 (|o|^2 + |c|^2), where sphere_disc's is ~ r^2),
 // hence the margin 2^-16 (|o|^2 + max(|c|^2 + r^2)): it covers the rounding of both forms (< 70 of the 256 ulp of that scale) and
 // | |d|^2 - 1 | <= 2^-19 of directions normalised with the 2-ulp MUFU reciprocal; tests/test_mask_margin.py measures
-// the slack.  cnt <= 32.
+// the slack.  The primitive's share of the margin, 2^-16 (|c|^2 + r^2), is folded into the table's w on upload, so one huge
+// sphere (the r = 1000 "floor") does not loosen the mask of the small ones (scenes/big_floor.json).  cnt <= 32.
 // Out of line on purpose: the scans call it from up to ten places (object runs, cluster bounds, cluster members,
 // generic-run bounds, CSG sphere runs; closest-hit and any-hit each); one copy keeps the kernel's hot code inside the
 // instruction cache (synthetic-A 2K 42.1 -> 30.4 ms, snorlax 4K 17.5 -> 16.8 ms).
@@ -216,7 +284,7 @@ template <bool C> __device__ __noinline__ uint32_t sphere_mask(const float4* bas
 #else
 template <bool C> __device__ __noinline__ uint32_t sphere_mask(const float4* base, int cnt, V3 o, V3 d) {
     const float oo = dot(o, o), od = dot(o, d);
-    const float bound = fmaf(-kMaskMargin, oo + c_hdr.mask_scale, oo) - 1e-30f;
+    const float bound = fmaf(-kMaskMargin, oo, oo) - 1e-30f;              // |o|^2's share; the primitive's is in the table
     const V3 m2o = mk(-2.f * o.x, -2.f * o.y, -2.f * o.z);
     uint32_t mask = 0;
     int k = 0;
@@ -349,7 +417,22 @@ template <bool C> __device__ Ivl leaf_interval(int li, V3 o, V3 d, unsigned& tes
 // Out of line on purpose: inlined into both scans it cost 800 B of spills at 128 registers; as a call the kernel fits 64
 // registers (4 CTAs = 32 warps per SM) with 1/4 of the spills (snorlax 4K 20.5 -> 17.1 ms, synthetic-B 547 -> 486 ms).
 struct ProgResult { Ivl v; unsigned tests; };       // tests: primitives examined (returned by value: a reference would pin the caller's counter to memory)
-template <bool C> __device__ __noinline__ ProgResult run_program(int first, int count, V3 o, V3 d) {
+
+// Candidates among n <= 32 consecutive sphere-like entries for THIS lane's ray: the warp's bundle cull first (geom: the
+// (centre, radius) entries, G: in shared memory), then, when many survive, the per-lane conservative mask over the mask
+// table entries `masks`.  The result is a superset of the entries whose exact discriminant is >= 0 (and, with `segment`,
+// whose roots can lie in (0, t_hi]).  Converged warp only.
+template <bool C, bool G> __device__ __forceinline__ uint32_t chunk_candidates(const float4* geom, const float4* masks, int n, V3 o, V3 d,
+                                                                               float t_hi, bool segment, unsigned& tests) {
+    uint32_t cand = cull<G>(geom, n, t_hi, segment, tests);
+    if (3 * __popc(cand) > n + 2) { tests += n; cand &= sphere_mask<C>(masks, n, o, d); }     // warp-uniform branch
+    return cand;
+}
+
+// `pred`: this lane wants the result.  coop: all 32 lanes of a converged warp walk the program together (the sphere runs
+// cull their leaves against the warp's bundle; lanes without `pred` only keep the others company); !coop: a per-lane call
+// from divergent code, nothing warp-level inside.
+template <bool C> __device__ __noinline__ ProgResult run_program(bool pred, const bool coop, int first, int count, V3 o, V3 d) {
     unsigned tests = 0;
     Ivl acc; acc.ok = false; acc.t0 = acc.t1 = 0.f; acc.c0 = acc.c1 = 0;
     Ivl stack[RT_MAX_CSG_STACK]; int sp = 0;
@@ -364,16 +447,19 @@ template <bool C> __device__ __noinline__ ProgResult run_program(int first, int 
             case RT_OP_XFIX: xfix(acc, arg); break;
             case RT_OP_COMBINE_SPHERES: {            // acc = (...(acc op s[first]) op s[first+1]) ... ) over plain spheres
                 const int first = (int)(arg & 0x3FFFu), n = (int)(arg >> 14);
-                tests += n;
                 for (int c0 = 0; c0 < n; c0 += 32) {
                     const int cnt = min(32, n - c0), base = first + c0;
-                    uint32_t mask = sphere_mask<C>(SV<C>::leaf_ptr(base), cnt, o, d);
+                    // leaf intervals live on the whole line (csg.cpp:61-163): cull on the lines, no window
+                    uint32_t mask;
+                    if (coop) mask = chunk_candidates<C, C>(SV<C>::leaf_geom_ptr(base), SV<C>::leaf_ptr(base), cnt, o, d, 0.f, false, tests);
+                    else { tests += cnt; mask = sphere_mask<C>(SV<C>::leaf_ptr(base), cnt, o, d); }
+                    if (!pred) mask = 0;
                     int pos = 0;
                     for (;;) {
                         const int k = mask ? (__ffs(mask) - 1) : cnt;          // next candidate, or the end of the chunk
                         float4 g = make_float4(0.f, 0.f, 0.f, 0.f); float hb = 0.f, disc = 0.f;
                         if (k < cnt) {
-                            mask &= mask - 1;
+                            mask &= mask - 1; ++tests;
                             g = SV<C>::leaf_geom(base + k);
                             disc = sphere_disc(g, o, d, hb);
                             if (disc < 0.f) continue;                          // the mask is conservative: k is a miss like pos..k-1
