@@ -231,8 +231,8 @@ int rt_debug_mt_jump_host(uint32_t seed, int log2_twists, uint32_t* out624);
 int rt_debug_device_layout(const rt_scene_desc* desc, int* order, int* n_runs, int* runs4, int* n_clusters, float* clusters4);
 
 /* HOST-ONLY: the table the device's conservative candidate scan reads (csrc/rt_device.cuh sphere_mask): for every entry of
- * the object, CSG-leaf and bound arrays, in that order, (cx, cy, cz, |c|^2 - r^2); *scale = max(|c|^2 + r^2) over the
- * finite sphere-like entries, the scale of the scan's rounding margin.  The scan only selects candidates for the exact
+ * the object, CSG-leaf and bound arrays, in that order, (cx, cy, cz, |c|^2 - r^2 - 2^-16 (|c|^2 + r^2)): the second term is
+ * the primitive's share of the scan's rounding margin; *scale = max(|c|^2 + r^2) over the finite sphere-like entries.  The scan only selects candidates for the exact
  * arithmetic of Sphere::intersect (geometry.cpp:12-37).  masks4 holds *n x 4 floats (n = objects + leaves + bounds);
  * pass masks4 = NULL to query n.                                                                              */
 int rt_debug_mask_table(const rt_scene_desc* desc, int* n, float* masks4, float* scale);

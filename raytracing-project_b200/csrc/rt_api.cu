@@ -60,6 +60,7 @@ struct rt_scene {
     bool flat{false};         // no ray can spawn a child (no reflective / refractive material, or recursion == 1)
     bool lockstep{false};     // flat scene with generic objects (CSG programs, wrapped primitives): see trace_flat
     bool bounces{false};      // most materials reflect or refract and medium.recursion >= 2: deep, uneven ray trees
+    bool clustered{false};    // a long run of plain spheres / pokeballs was reordered into spatial clusters (kernel variant K)
     size_t smem_bytes{0};
     std::vector<float4> obj_geom, leaf_geom, pokeballs, affines, materials, lights, fallbacks, clusters, masks;
     float mask_scale{0.f};
@@ -89,7 +90,6 @@ int4 meta_of(const rt_prim& p) { return make_int4((p.kind & 0xff) | (p.flags << 
 // the scan order and exact ties are resolved by JSON index on the device (obj_orig).
 constexpr int kClusterSize = 16;      // the device code shifts by 4
 constexpr int kClusterMinRun = 48;
-constexpr int kGenericBoundMinRun = 8;  // runs of generic objects this long get a per-object world bound
 
 void split_run(std::vector<int>& idx, int lo, int hi, const rt_prim* objs) {
     if (hi - lo <= kClusterSize) return;
@@ -152,6 +152,7 @@ void build_host_arrays(const rt_scene_desc& d, rt_scene& s) {
             if (est < 0.35 * (j - i)) {
                 order.swap(trial);
                 clustered.push_back({i, j - i, (int)s.clusters.size()});
+                s.clustered = true;
                 s.clusters.insert(s.clusters.end(), bounds.begin(), bounds.end());
             }
         }
@@ -200,9 +201,10 @@ void build_host_arrays(const rt_scene_desc& d, rt_scene& s) {
         if (!plain) {                      // maximal run of generic objects (CSG programs, transform-wrapped / affine primitives)
             int j = i; while (j < d.n_objects && !(d.objects[j].flags == 0 && d.objects[j].kind != RT_PRIM_PROGRAM)) ++j;
             int ctab = 0;
-            if (j - i >= kGenericBoundMinRun) {
-                // one conservative WORLD bounding sphere per object (R = inf: unknown), scanned with the candidate mask
-                // before the object itself is looked at
+            {
+                // one conservative WORLD bounding sphere per object (R = inf: unknown): the scans cull the bounds against the
+                // warp's ray bundle (or, for incoherent bundles, scan them with the candidate mask) before the object itself
+                // is looked at
                 ctab = (int)s.clusters.size() + 1;
                 for (int k = i; k < j; ++k) {
                     const rt_prim& q = d.objects[k];
@@ -226,12 +228,13 @@ void build_host_arrays(const rt_scene_desc& d, rt_scene& s) {
         s.runs.push_back(make_int4(kind, i, j - i, ctab));
         i = j;
     }
-    // Mask table of sphere_mask: (c, |c|^2 - r^2) for every entry of obj_geom | leaf_geom | clusters (entries that are not
-    // sphere-like are never scanned through it), and the scale of its rounding margin, max(|c|^2 + r^2) over finite entries.
+    // Mask table of sphere_mask: (c, |c|^2 - r^2 - 2^-16 (|c|^2 + r^2)) for every entry of obj_geom | leaf_geom | clusters
+    // (entries that are not sphere-like are never scanned through it): the primitive's own share of the scan's rounding
+    // margin is folded into w, so the margin is per primitive.  `scale` = max(|c|^2 + r^2) is only reported.
     double scale = 0.0;
     auto add = [&](const float4& g, bool scanned) {
         const double cc = (double)g.x * g.x + (double)g.y * g.y + (double)g.z * g.z, rr = (double)g.w * g.w;
-        s.masks.push_back(make_float4(g.x, g.y, g.z, (float)(cc - rr)));
+        s.masks.push_back(make_float4(g.x, g.y, g.z, (float)((cc - rr) - (double)rtd::kMaskMargin * (cc + rr))));
         if (scanned && std::isfinite(cc + rr)) scale = std::max(scale, cc + rr);
     };
     auto sphere_like = [](const int4& m) { return (m.x & 0xff) != RT_PRIM_HALFSPACE && !((m.x >> 8) & RT_FLAG_AFFINE); };
@@ -327,7 +330,7 @@ int rt_scene_upload(const rt_scene_desc* d, rt_scene** out) {
     h.masks = s->d_masks; h.mask_scale = s->mask_scale;
     s->width = d->width; s->height = d->height;
     h.n_leaves = d->n_leaves; h.n_ops = d->n_ops;
-    h.off_leaf_geom = s->clusters.empty() ? d->n_objects : 0;        // scenes with bounds read top-level geometry from global memory
+    h.off_leaf_geom = s->clustered ? 0 : d->n_objects;               // scenes with clustered runs read top-level geometry from global memory
     h.off_leaf_meta = h.off_leaf_geom + d->n_leaves; h.off_runs = h.off_leaf_meta + d->n_leaves;
     h.off_lights = h.off_runs + (int)s->runs.size();
     h.off_clusters = h.off_lights + 2 * h.n_lights;
@@ -509,8 +512,8 @@ int launch_frame(rt_scene* s, int mode, int rank, int world, uchar4* rgba8, floa
         { int rc2 = grow(&g_ctx.d_gbuf, &g_ctx.gbuf_cap, (size_t)npx * sizeof(rtd::GBuf)); if (rc2) return rc2; }
         const unsigned blocks = (unsigned)((npx + 255) / 256);
         // kernel variant: <scene staged in shared memory, scene has clustered runs>
-        auto paper = s->fits_const ? (s->clusters.empty() ? rtd::paper_gbuffer_kernel<true, false> : rtd::paper_gbuffer_kernel<true, true>)
-                                   : (s->clusters.empty() ? rtd::paper_gbuffer_kernel<false, false> : rtd::paper_gbuffer_kernel<false, true>);
+        auto paper = s->fits_const ? (!s->clustered ? rtd::paper_gbuffer_kernel<true, false> : rtd::paper_gbuffer_kernel<true, true>)
+                                   : (!s->clustered ? rtd::paper_gbuffer_kernel<false, false> : rtd::paper_gbuffer_kernel<false, true>);
         paper<<<blocks, 256, s->fits_const ? s->smem_bytes : 0, st>>>(g_ctx.d_gbuf, ids, g_ctx.counters, rank, world);
         rtd::paper_post_kernel<<<blocks, 256, 0, st>>>(g_ctx.d_gbuf, rgba8, rgbf, s->width, s->height, rank, world);
         CU(cudaGetLastError());
@@ -526,7 +529,7 @@ int launch_frame(rt_scene* s, int mode, int rank, int world, uchar4* rgba8, floa
     prm.n_local_tiles = (int)local; prm.rank = rank; prm.world = world; prm.n_pixels = npx; prm.lockstep = s->lockstep ? 1 : 0;
     CU(cudaMemsetAsync(g_ctx.tile_counter, 0, sizeof(unsigned), st));
     // kernel variant: <scene staged in shared memory, scene has bounds>; ray trees deeper than 1 -> wavefront kernel
-    const bool kk = !s->clusters.empty();
+    const bool kk = s->clustered;
     auto kernel = s->bounces
         ? (s->fits_const ? (kk ? rtd::render_wavefront_kernel<true, true> : rtd::render_wavefront_kernel<true, false>)
                          : (kk ? rtd::render_wavefront_kernel<false, true> : rtd::render_wavefront_kernel<false, false>))

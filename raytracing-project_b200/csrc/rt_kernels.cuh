@@ -100,7 +100,7 @@ struct RenderParams {
     unsigned* tile_counter;       // dynamic tile scheduler
     float4* wave_state;           // wavefront kernel: per CTA, per sample of its tile: ray + pending parents
     int n_local_tiles, rank, world;
-    int lockstep;                 // flat scenes: CTA barrier before every light (trace_flat)
+    int lockstep;                 // flat scenes: CTA barrier before every light (shade)
     long long n_pixels;
 };
 
@@ -138,7 +138,7 @@ __device__ __forceinline__ void flush_counters(const Counters& c, unsigned long 
 #endif
 constexpr int kRenderThreads = 256;
 
-// F ("flat"): no ray of the scene can spawn a child, see trace_flat.
+// F ("flat"): no ray of the scene can spawn a child, see ray_step.
 template <bool C, bool K, bool F>
 __global__ void __launch_bounds__(kRenderThreads, RT_MIN_BLOCKS) render_standard_kernel(RenderParams prm) {
     // raw generator words: [0, kN) the tile's checkpoint, then the 8 blocks it yields (tempered on use)
@@ -167,7 +167,7 @@ __global__ void __launch_bounds__(kRenderThreads, RT_MIN_BLOCKS) render_standard
         // --- one sample per thread; 8 consecutive lanes share a pixel.  A warp takes the tile's 39 groups of 32 samples
         // from a shared counter, so a warp that drew expensive samples traces fewer groups and the barrier at the end of
         // the tile waits for one group at most.  In lockstep the groups are dealt statically (every warp must run the same
-        // number of rounds: trace_flat has barriers inside). ---
+        // number of rounds: shade has barriers inside). ---
         const long long pix0 = tile * mt::kPixelsPerTile;
 #pragma unroll 1
         for (int round = 0;; ++round) {
@@ -195,10 +195,9 @@ __global__ void __launch_bounds__(kRenderThreads, RT_MIN_BLOCKS) render_standard
                 const double sx = ((double)x + 0.5 + jx) / (double)nx, sy = ((double)y + 0.5 + jy) / (double)ny;
                 camera_ray(sx, sy, o, d);
             }
-            if (F || active) {
+            {   // all 32 lanes trace together (rt_trace.cuh); a lane without a sample keeps the others company
                 Hit ph; bool phit;
-                if (F) { c = trace_flat<C, K>(active, prm.lockstep != 0, o, d, ph, phit, cnt); if (!active) c = rgb(0.f, 0.f, 0.f); }
-                else c = trace<C, K>(o, d, &ph, &phit, cnt);
+                c = trace<C, K, F, RT_MAX_RECURSION>(active, prm.lockstep != 0, o, d, ph, phit, cnt);
                 if (active && prm.ids) prm.ids[((long long)yy * nx + x) * 8 + (j & 7)] = phit ? ph.code : -1;
             }
 #pragma unroll
@@ -329,22 +328,28 @@ __global__ void __launch_bounds__(kRenderThreads, RT_WAVE_BLOCKS) render_wavefro
                     asm volatile("prefetch.global.L1 [%0];" :: "l"(nx_state));
                 }
                 k += (int)lane;
+                const bool valid = k < n;                            // the 32 lanes step together; lanes past the end keep company
                 bool more = false; int sid = 0;
-                if (k < n) {
+                float4* sp = my_state;
+                V3 o = mk(0.f, 0.f, 0.f), d = mk(0.f, 1.f, 0.f);
+                int depth = 0;
+                if (valid) {
                     sid = s_list[q][k];
-                    float4* sp = my_state + (size_t)sid * stride;
+                    sp = my_state + (size_t)sid * stride;
                     const float4 a = sp[0], b = sp[1];
-                    V3 o = mk(a.x, a.y, a.z), d = mk(a.w, b.x, b.y);
-                    int depth = __float_as_int(b.z);
-                    const bool primary = depth == 0;                 // only the camera ray is traced at depth 0
-                    RGBf c = rgb(0.f, 0.f, 0.f);
-                    Hit ph; bool phit = false;
-                    if (limit <= 0) {                                // tracer.cpp:26: black, but the id buffer is still defined
-                        ++cnt.primary;
-                        if (prm.ids) phit = closest_hit<C, K>(o, d, 1e-4f, kInf, ph, cnt);
-                    } else {
-                        more = !advance_ray<C, K>(o, d, depth, sp + 2, c, ph, phit, cnt);
-                    }
+                    o = mk(a.x, a.y, a.z); d = mk(a.w, b.x, b.y);
+                    depth = __float_as_int(b.z);
+                }
+                const bool primary = depth == 0;                     // only the camera ray is traced at depth 0
+                RGBf c = rgb(0.f, 0.f, 0.f);
+                Hit ph; bool phit = false;
+                if (limit <= 0) {                                    // tracer.cpp:26: black, but the id buffer is still defined
+                    if (valid) ++cnt.primary;
+                    phit = closest_hit<C, K>(valid && prm.ids != nullptr, o, d, 1e-4f, kInf, ph, cnt);
+                } else {
+                    more = !ray_step<C, K, false>(valid, false, o, d, depth, sp + 2, c, ph, phit, cnt) && valid;
+                }
+                if (valid) {
                     if (primary && prm.ids) {
                         const int t = sid / mt::kSamplesPerTile, j = sid - t * mt::kSamplesPerTile;
                         const long long tile = (long long)prm.rank + (long long)s_tile[t] * prm.world;
@@ -420,25 +425,28 @@ __global__ void __launch_bounds__(256, RT_PAPER_BLOCKS) paper_gbuffer_kernel(GBu
     const long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     Counters cnt = {0, 0, 0, 0};
     stage_scene<C>();
-    if (q < (long long)nx * ny) {
-        const int y = (int)(q / nx), x = (int)(q - (long long)y * nx);
-        const bool own = paper_row_owned(y, rank, world);
-        const bool need = own || (y > 0 && paper_row_owned(y - 1, rank, world)) || (y + 1 < ny && paper_row_owned(y + 1, rank, world));
-        if (need) {
-            // Camera::generate_ray (camera.h:44-58): pixel centre, j flipped
-            const double sx = ((double)x + 0.5) / (double)nx, sy = ((double)(ny - 1 - y) + 0.5) / (double)ny;
-            V3 o, d; camera_ray(sx, sy, o, d);
-            Hit h; GBuf g;
-            ++cnt.primary;
-            const bool hit = closest_hit<C, K>(o, d, 1e-4f, kInf, h, cnt);      // tracer.cpp:111-120
-            g.hit = hit; g.t = hit ? h.t : kInf; g.mat = hit ? h.mat : -1; g.code = hit ? h.code : -1;
-            g.nx = hit ? h.n.x : 0.f; g.ny = hit ? h.n.y : 0.f; g.nz = hit ? h.n.z : 0.f;
-            RGBf base = rgb(1.f, 1.f, 1.f);
-            if (hit && own) base = shade<C, K>(h, madd(o, d, h.t), normalized(neg(d)), cnt);
-            g.lum = 0.299f * base.r + 0.587f * base.g + 0.114f * base.b;      // tracer.cpp:123-125
-            gb[q] = g;
-            if (ids && own) ids[q] = g.code;
-        }
+    // the 32 pixels of a warp trace together (rt_trace.cuh); pixels past the end and rows this rank does not need keep company
+    const bool inside = q < (long long)nx * ny;
+    const int y = inside ? (int)(q / nx) : 0, x = inside ? (int)(q - (long long)y * nx) : 0;
+    const bool own = inside && paper_row_owned(y, rank, world);
+    const bool need = inside && (own || (y > 0 && paper_row_owned(y - 1, rank, world)) || (y + 1 < ny && paper_row_owned(y + 1, rank, world)));
+    // Camera::generate_ray (camera.h:44-58): pixel centre, j flipped
+    const double sx = ((double)x + 0.5) / (double)nx, sy = ((double)(ny - 1 - y) + 0.5) / (double)ny;
+    V3 o, d; camera_ray(sx, sy, o, d);
+    Hit h; h.mat = -1; h.t = 0.f; h.n = mk(0.f, 1.f, 0.f); h.front = true; h.code = -1;
+    if (need) ++cnt.primary;
+    const bool hit = closest_hit<C, K>(need, o, d, 1e-4f, kInf, h, cnt);      // tracer.cpp:111-120
+    const bool lit = hit && own && h.mat >= 0;
+    const RGBf lum = shade<C, K>(lit, false, h, madd(o, d, h.t), normalized(neg(d)), cnt);
+    if (need) {
+        GBuf g;
+        g.hit = hit; g.t = hit ? h.t : kInf; g.mat = hit ? h.mat : -1; g.code = hit ? h.code : -1;
+        g.nx = hit ? h.n.x : 0.f; g.ny = hit ? h.n.y : 0.f; g.nz = hit ? h.n.z : 0.f;
+        RGBf base = rgb(1.f, 1.f, 1.f);
+        if (hit && own) base = lit ? lum : rgb(1.f, 0.f, 1.f);              // shading.cpp:33: magenta without a material
+        g.lum = 0.299f * base.r + 0.587f * base.g + 0.114f * base.b;      // tracer.cpp:123-125
+        gb[q] = g;
+        if (ids && own) ids[q] = g.code;
     }
     flush_counters(cnt, counters);
 }
@@ -502,15 +510,17 @@ __global__ void __launch_bounds__(128) trace_rays_kernel(const double* rays, dou
     constexpr bool K = true;            // clustered runs supported; specialisation does not matter here
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     stage_scene<C>();
-    if (i >= n) return;
-    const double* q = rays + (size_t)i * 6;
+    const bool active = i < n;                   // the 32 lanes trace together; lanes past the end keep company
+    const double* q = rays + (size_t)(active ? i : 0) * 6;
     double dx = q[3], dy = q[4], dz = q[5];
     const double L = sqrt(dx * dx + dy * dy + dz * dz);
     if (L > 1e-6) { dx /= L; dy /= L; dz /= L; } else { dx = 0; dy = 1; dz = 0; }
     const V3 o = mk((float)q[0], (float)q[1], (float)q[2]), d = mk((float)dx, (float)dy, (float)dz);
     Counters cnt = {0, 0, 0, 0};
     Hit h; bool hit;
-    const RGBf c = trace<C, K>(o, d, &h, &hit, cnt);
+    const RGBf c = trace<C, K, false, RT_MAX_RECURSION>(active, false, o, d, h, hit, cnt);
+    const bool occ = occluded<C, K>(active, o, d, 1e-3f, 5.0f, cnt);
+    if (!active) return;
     double* r = out + (size_t)i * 16;
     for (int k = 0; k < 16; ++k) r[k] = 0.0;
     r[0] = hit ? 1.0 : 0.0;
@@ -521,7 +531,7 @@ __global__ void __launch_bounds__(128) trace_rays_kernel(const double* rays, dou
     }
     r[9] = hit ? (double)h.code : -1.0;
     r[10] = c.r; r[11] = c.g; r[12] = c.b;
-    r[13] = occluded<C, K>(o, d, 1e-3f, 5.0f, cnt) ? 1.0 : 0.0;
+    r[13] = occ ? 1.0 : 0.0;
     r[14] = (double)cnt.tests; r[15] = (double)(cnt.shadow + cnt.secondary);
 }
 

@@ -54,9 +54,20 @@ def test_cluster_bounds_contain_their_members(rt):
 
 
 def test_dense_or_short_runs_are_not_clustered(rt):
-    for name in ("synthetic_b_small", "snorlax_small", "penguin_small"):
-        _, runs, clusters = rt.load_scene_from_json(scene_path(name)).device_layout()
-        assert len(clusters) == 0 and all(r[3] == 0 for r in runs.tolist())
+    """Sphere / pokeball runs that are short or dense stay in JSON order without cluster bounds; every generic object
+    (CSG program, wrapped / affine primitive) has exactly one world bound (R = inf when nothing is known)."""
+    for name in ("synthetic_b_small", "snorlax_small", "penguin_small", "quirks"):
+        sc = rt.load_scene_from_json(scene_path(name))
+        order, runs, clusters = sc.device_layout()
+        assert order.tolist() == list(range(sc.desc.n_objects))
+        n_generic = sum(r[2] for r in runs.tolist() if r[0] == 3)
+        assert len(clusters) == n_generic
+        for kind, first, count, ctab in runs.tolist():
+            assert (ctab > 0) == (kind == 3)
+    objs = rt.load_scene_from_json(scene_path("snorlax_small")).objects()
+    _, runs, clusters = rt.load_scene_from_json(scene_path("snorlax_small")).device_layout()
+    g = [r for r in runs.tolist() if r[0] == 3][0]
+    assert list(clusters[g[3] - 1]) == pytest.approx(list(objs[g[1]].geom)), "the program's bound is its compiled bounding sphere"
 
 
 def test_layout_of_an_empty_and_a_non_finite_scene(rt):
