@@ -40,7 +40,7 @@ struct Context {
 };
 Context g_ctx;
 // Test hooks (rt_debug_set_option): -1 = the library's own choice, 0 / 1 = forced.  Never read from the environment.
-struct DebugOptions { int flat{-1}, lockstep{-1}, wavefront{-1}, global_scene{-1}, mt_sequential{-1}; };
+struct DebugOptions { int flat{-1}, cull{-1}, wavefront{-1}, global_scene{-1}, mt_sequential{-1}; };
 DebugOptions g_opts;
 constexpr size_t kSceneSmemBudget = 80 * 1024;   // + 25 KB of MT19937 buffers: two CTAs per SM still fit in 227 KB
 
@@ -58,17 +58,17 @@ struct rt_scene {
     rtd::SceneHeader hdr{};
     bool fits_const{false};   // scanned arrays fit the shared-memory budget (staged per CTA)
     bool flat{false};         // no ray can spawn a child (no reflective / refractive material, or recursion == 1)
-    bool lockstep{false};     // flat scene with generic objects (CSG programs, wrapped primitives): see trace_flat
     bool bounces{false};      // most materials reflect or refract and medium.recursion >= 2: deep, uneven ray trees
     bool clustered{false};    // a long run of plain spheres / pokeballs was reordered into spatial clusters (kernel variant K)
     size_t smem_bytes{0};
-    std::vector<float4> obj_geom, leaf_geom, pokeballs, affines, materials, lights, fallbacks, clusters, masks;
+    std::vector<float4> obj_geom, leaf_geom, pokeballs, affines, materials, lights, fallbacks, clusters, masks, cull_geom;
+    int cull_words{0}, cull_cl_word{0}, cull_leaf_word{0};
     float mask_scale{0.f};
     std::vector<int4> obj_meta, leaf_meta, runs;
     std::vector<int> obj_orig;
     std::vector<uint32_t> ops;
     float4 *d_obj_geom{nullptr}, *d_leaf_geom{nullptr}, *d_pokeballs{nullptr}, *d_affines{nullptr}, *d_materials{nullptr},
-           *d_lights{nullptr}, *d_fallbacks{nullptr}, *d_clusters{nullptr}, *d_masks{nullptr};
+           *d_lights{nullptr}, *d_fallbacks{nullptr}, *d_clusters{nullptr}, *d_masks{nullptr}, *d_cull_geom{nullptr};
     int* d_obj_orig{nullptr};
     int4 *d_obj_meta{nullptr}, *d_leaf_meta{nullptr}, *d_runs{nullptr};
     uint32_t* d_ops{nullptr};
@@ -242,6 +242,28 @@ void build_host_arrays(const rt_scene_desc& d, rt_scene& s) {
     for (size_t i = 0; i < s.leaf_geom.size(); ++i) add(s.leaf_geom[i], sphere_like(s.leaf_meta[i]));
     for (const float4& g : s.clusters) add(g, true);
     s.mask_scale = (float)std::min(scale * (1.0 + 1e-6), 3.0e38);
+    // Round-level culling table (rt_cull.cuh, rt_device.cuh cand_build): (centre, radius) of every top-level object, every
+    // bound (cluster of a clustered run / world bound of a generic object) and every CSG leaf, radius = inf where nothing can
+    // be said (half-spaces, affine primitives, programs without a bound: always candidates); each section padded to a multiple
+    // of 32 entries with w < 0 (never candidates).  Members of generic runs are represented by their bound, so their object
+    // entry is inf as well (the scans never ask for it).
+    const float inf = std::numeric_limits<float>::infinity();
+    auto pad32 = [&]() { while (s.cull_geom.size() % 32) s.cull_geom.push_back(make_float4(0.f, 0.f, 0.f, -1.f)); };
+    auto finite4 = [](const float4& g) { return std::isfinite(g.x) && std::isfinite(g.y) && std::isfinite(g.z) && std::isfinite(g.w); };
+    for (size_t i = 0; i < s.obj_geom.size(); ++i) {
+        const float4 g = s.obj_geom[i]; const int4 m = s.obj_meta[i];
+        const bool plain = (m.x >> 8) == 0 && ((m.x & 0xff) == RT_PRIM_SPHERE || (m.x & 0xff) == RT_PRIM_POKEBALL) && finite4(g);
+        s.cull_geom.push_back(plain ? make_float4(g.x, g.y, g.z, std::fabs(g.w)) : make_float4(0.f, 0.f, 0.f, inf));
+    }
+    pad32(); s.cull_cl_word = (int)(s.cull_geom.size() / 32);
+    for (const float4& g : s.clusters) s.cull_geom.push_back(finite4(g) && g.w >= 0.f ? g : make_float4(0.f, 0.f, 0.f, inf));
+    pad32(); s.cull_leaf_word = (int)(s.cull_geom.size() / 32);
+    for (size_t i = 0; i < s.leaf_geom.size(); ++i) {
+        const float4 g = s.leaf_geom[i]; const int4 m = s.leaf_meta[i];
+        const bool plain = (m.x & 0xff) == RT_PRIM_SPHERE && !((m.x >> 8) & (RT_FLAG_AFFINE | RT_FLAG_NEVER)) && finite4(g);
+        s.cull_geom.push_back(plain ? make_float4(g.x, g.y, g.z, std::fabs(g.w)) : make_float4(0.f, 0.f, 0.f, inf));
+    }
+    pad32(); s.cull_words = (int)(s.cull_geom.size() / 32);
 }
 
 }  // namespace
@@ -272,15 +294,15 @@ int rt_init(int device) {
     CU(cudaMemcpy(g_ctx.mt_resume, seed, sizeof(seed), cudaMemcpyHostToDevice));
     g_ctx.mt_tiles = 0; g_ctx.mt_capacity = 0; g_ctx.mt_table = nullptr; g_ctx.const_owner = nullptr;
     g_ctx.mt_resume_tiles = 0; g_ctx.d_jump_poly = nullptr;
-    CU(cudaFuncSetAttribute(rtd::render_standard_kernel<true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget));
-    CU(cudaFuncSetAttribute(rtd::render_standard_kernel<true, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget));
-    CU(cudaFuncSetAttribute(rtd::render_standard_kernel<true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget));
-    CU(cudaFuncSetAttribute(rtd::render_standard_kernel<true, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget));
-    CU(cudaFuncSetAttribute(rtd::render_wavefront_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget));
-    CU(cudaFuncSetAttribute(rtd::render_wavefront_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget));
-    CU(cudaFuncSetAttribute(rtd::paper_gbuffer_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget));
-    CU(cudaFuncSetAttribute(rtd::paper_gbuffer_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget));
-    CU(cudaFuncSetAttribute(rtd::trace_rays_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget));
+    CU(cudaFuncSetAttribute(rtd::render_standard_kernel<true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget + 4096));
+    CU(cudaFuncSetAttribute(rtd::render_standard_kernel<true, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget + 4096));
+    CU(cudaFuncSetAttribute(rtd::render_standard_kernel<true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget + 4096));
+    CU(cudaFuncSetAttribute(rtd::render_standard_kernel<true, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget + 4096));
+    CU(cudaFuncSetAttribute(rtd::render_wavefront_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget + 4096));
+    CU(cudaFuncSetAttribute(rtd::render_wavefront_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget + 4096));
+    CU(cudaFuncSetAttribute(rtd::paper_gbuffer_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget + 4096));
+    CU(cudaFuncSetAttribute(rtd::paper_gbuffer_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget + 4096));
+    CU(cudaFuncSetAttribute(rtd::trace_rays_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget + 4096));
     g_ctx.ready = true;
     return RT_OK;
 }
@@ -317,7 +339,8 @@ int rt_scene_upload(const rt_scene_desc* d, rt_scene** out) {
         (rc = upload(s->ops, &s->d_ops)) || (rc = upload(s->materials, &s->d_materials)) ||
         (rc = upload(s->lights, &s->d_lights)) || (rc = upload(s->fallbacks, &s->d_fallbacks)) ||
         (rc = upload(s->runs, &s->d_runs)) || (rc = upload(s->clusters, &s->d_clusters)) ||
-        (rc = upload(s->obj_orig, &s->d_obj_orig)) || (rc = upload(s->masks, &s->d_masks))) { free_scene_locked(s); return rc; }
+        (rc = upload(s->obj_orig, &s->d_obj_orig)) || (rc = upload(s->masks, &s->d_masks)) ||
+        (rc = upload(s->cull_geom, &s->d_cull_geom))) { free_scene_locked(s); return rc; }
     rtd::SceneHeader& h = s->hdr;
     for (int k = 0; k < 3; ++k) { h.eye[k] = d->eye[k]; h.P[k] = d->screen_p[k]; h.bg[k] = d->background[k]; }
     h.lx = d->lx; h.ly = d->ly; h.nx = d->width; h.ny = d->height;
@@ -337,20 +360,23 @@ int rt_scene_upload(const rt_scene_desc* d, rt_scene** out) {
     h.off_masks = h.off_clusters + h.n_clusters;
     h.off_ops_bytes = 16 * (h.off_masks + (int)s->masks.size());
     h.smem_bytes = h.off_ops_bytes + 4 * d->n_ops;
-    s->smem_bytes = (size_t)h.smem_bytes;
-    s->fits_const = s->smem_bytes <= kSceneSmemBudget;
+    s->fits_const = (size_t)h.smem_bytes <= kSceneSmemBudget;
     // Wavefront kernel only where most surfaces spawn secondary rays: its per-sample state traffic costs ~10 % on scenes
     // whose ray trees are mostly depth 1 (snorlax with one reflective sphere), and gains ~6 % on the all-glass lattice.
     int n_bounce = 0;
     for (int i = 0; i < d->n_materials; ++i) n_bounce += (d->materials[i].kr > 0.f || d->materials[i].kt > 0.f) ? 1 : 0;
     s->flat = d->recursion >= 1 && (n_bounce == 0 || d->recursion == 1);
     if (g_opts.flat == 0) s->flat = false;                                  // test hook: generic loop on a flat scene
-    s->lockstep = s->flat && (d->n_ops > 0 || d->n_affines > 0);
-    if (g_opts.lockstep >= 0) s->lockstep = s->flat && g_opts.lockstep == 1;  // test hook
     s->bounces = d->recursion >= 2 && d->n_materials > 0 && 2 * n_bounce >= d->n_materials;
     if (g_opts.wavefront >= 0) s->bounces = g_opts.wavefront == 1;          // test hook: either kernel on any scene
     if (g_opts.global_scene == 1) s->fits_const = false;                    // test hook: the global-memory path on any scene
-    *out = s;
+    // Round-level culling: masks of (1 + kMaxListLights) bundles behind the staged scene (or alone, on the global path).
+    // Scenes whose table is too long for a CTA to cull per round (> kMaxCullWords x 32 entries) scan without masks.
+    constexpr int kMaxCullWords = 96;
+    const bool cull = s->cull_words > 0 && s->cull_words <= kMaxCullWords && g_opts.cull != 0;
+    h.cull_geom = s->d_cull_geom; h.cull_words = cull ? s->cull_words : 0; h.cull_cl_word = s->cull_cl_word; h.cull_leaf_word = s->cull_leaf_word;
+    h.off_cand_bytes = s->fits_const ? ((h.smem_bytes + 15) & ~15) : 0;
+    s->smem_bytes = (size_t)h.off_cand_bytes + (cull ? sizeof(rtd::CandShared) + (size_t)(1 + rtd::kMaxListLights) * s->cull_words * 4 : 0);    *out = s;
     return RT_OK;
 }
 
@@ -364,7 +390,7 @@ int rt_debug_set_option(const char* name, int value) {
     if (!name) return fail(RT_ERR_ARG, "rt_debug_set_option: null name");
     std::lock_guard<std::mutex> lk(g_ctx.mu);
     const std::string n(name);
-    int* slot = n == "flat" ? &g_opts.flat : n == "lockstep" ? &g_opts.lockstep : n == "wavefront" ? &g_opts.wavefront
+    int* slot = n == "flat" ? &g_opts.flat : n == "cull" ? &g_opts.cull : n == "wavefront" ? &g_opts.wavefront
               : n == "global_scene" ? &g_opts.global_scene : n == "mt_sequential" ? &g_opts.mt_sequential : nullptr;
     if (!slot) return fail(RT_ERR_ARG, "rt_debug_set_option: unknown option " + n);
     *slot = value < 0 ? -1 : (value ? 1 : 0);
@@ -378,7 +404,7 @@ void free_scene_locked(rt_scene* s) {
     if (g_ctx.const_owner == s) g_ctx.const_owner = nullptr;
     cudaFree(s->d_obj_geom); cudaFree(s->d_obj_meta); cudaFree(s->d_leaf_geom); cudaFree(s->d_leaf_meta);
     cudaFree(s->d_pokeballs); cudaFree(s->d_affines); cudaFree(s->d_ops); cudaFree(s->d_materials);
-    cudaFree(s->d_lights); cudaFree(s->d_fallbacks); cudaFree(s->d_runs); cudaFree(s->d_clusters); cudaFree(s->d_obj_orig); cudaFree(s->d_masks);
+    cudaFree(s->d_lights); cudaFree(s->d_fallbacks); cudaFree(s->d_runs); cudaFree(s->d_clusters); cudaFree(s->d_obj_orig); cudaFree(s->d_masks); cudaFree(s->d_cull_geom);
     delete s;
 }
 }  // namespace
@@ -514,7 +540,7 @@ int launch_frame(rt_scene* s, int mode, int rank, int world, uchar4* rgba8, floa
         // kernel variant: <scene staged in shared memory, scene has clustered runs>
         auto paper = s->fits_const ? (!s->clustered ? rtd::paper_gbuffer_kernel<true, false> : rtd::paper_gbuffer_kernel<true, true>)
                                    : (!s->clustered ? rtd::paper_gbuffer_kernel<false, false> : rtd::paper_gbuffer_kernel<false, true>);
-        paper<<<blocks, 256, s->fits_const ? s->smem_bytes : 0, st>>>(g_ctx.d_gbuf, ids, g_ctx.counters, rank, world);
+        paper<<<blocks, 256, s->smem_bytes, st>>>(g_ctx.d_gbuf, ids, g_ctx.counters, rank, world);
         rtd::paper_post_kernel<<<blocks, 256, 0, st>>>(g_ctx.d_gbuf, rgba8, rgbf, s->width, s->height, rank, world);
         CU(cudaGetLastError());
         if (n_tiles_out) *n_tiles_out = (s->height + rtd::kPaperRows - 1) / rtd::kPaperRows;
@@ -526,7 +552,7 @@ int launch_frame(rt_scene* s, int mode, int rank, int world, uchar4* rgba8, floa
     rtd::RenderParams prm{};
     prm.mt_table = g_ctx.mt_table; prm.rgba8 = rgba8; prm.rgbf = rgbf; prm.ids = ids;
     prm.counters = g_ctx.counters; prm.tile_counter = g_ctx.tile_counter;
-    prm.n_local_tiles = (int)local; prm.rank = rank; prm.world = world; prm.n_pixels = npx; prm.lockstep = s->lockstep ? 1 : 0;
+    prm.n_local_tiles = (int)local; prm.rank = rank; prm.world = world; prm.n_pixels = npx;
     CU(cudaMemsetAsync(g_ctx.tile_counter, 0, sizeof(unsigned), st));
     // kernel variant: <scene staged in shared memory, scene has bounds>; ray trees deeper than 1 -> wavefront kernel
     const bool kk = s->clustered;
@@ -537,7 +563,7 @@ int launch_frame(rt_scene* s, int mode, int rank, int world, uchar4* rgba8, floa
                                    : (kk ? rtd::render_standard_kernel<false, true, true> : rtd::render_standard_kernel<false, false, true>))
                   : (s->fits_const ? (kk ? rtd::render_standard_kernel<true, true, false> : rtd::render_standard_kernel<true, false, false>)
                                    : (kk ? rtd::render_standard_kernel<false, true, false> : rtd::render_standard_kernel<false, false, false>));
-    const size_t smem = s->fits_const ? s->smem_bytes : 0;
+    const size_t smem = s->smem_bytes;
     int per_sm = 0;
     const int threads = rtd::kRenderThreads;
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem));
@@ -705,7 +731,7 @@ int rt_trace_rays(rt_scene* s, int n, const double* rays, double* out) {
         if (e0 != cudaSuccess) { cudaFree(d_in); return fail(RT_ERR_CUDA, std::string("rt_trace_rays: ") + cudaGetErrorString(e0)); }
     }
     if (s->fits_const) rtd::trace_rays_kernel<true><<<(n + 127) / 128, 128, s->smem_bytes, st>>>(d_in, d_out, n);
-    else rtd::trace_rays_kernel<false><<<(n + 127) / 128, 128, 0, st>>>(d_in, d_out, n);
+    else rtd::trace_rays_kernel<false><<<(n + 127) / 128, 128, s->smem_bytes, st>>>(d_in, d_out, n);
     cudaError_t e = cudaGetLastError();
     if (e == cudaSuccess) e = cudaMemcpyAsync(out, d_out, (size_t)n * 16 * sizeof(double), cudaMemcpyDeviceToHost, st);
     if (e == cudaSuccess) e = cudaStreamSynchronize(st);

@@ -39,6 +39,11 @@ struct SceneHeader {
     const float4* clusters;     // bounding sphere of every 16 consecutive primitives of a clustered run
     const int* obj_orig;        // JSON index of device object i (clustered runs are reordered spatially)
     const float4* masks;        // (c.xyz, |c|^2 - r^2 - 2^-16 (|c|^2 + r^2)) of every entry of obj_geom, leaf_geom, clusters (in that order)
+    // round-level culling (rt_cull.cuh): (centre, radius | inf) of objects | bounds | leaves, every section padded to a
+    // multiple of 32 with w < 0; candidate bit of object i: cull_obj_word*32 + i (= i), of bound i: cull_cl_word*32 + i, ...
+    const float4* cull_geom;
+    int cull_words, cull_cl_word, cull_leaf_word;     // words per bundle (0: scene not culled), first word of the bound / leaf section
+    int off_cand_bytes;                               // CandShared + masks in dynamic shared memory
 };
 
 enum { RUN_SPHERE = 0, RUN_HALFSPACE = 1, RUN_POKEBALL = 2, RUN_GENERIC = 3 };
@@ -73,10 +78,6 @@ template <bool C> struct SV {
     static __device__ __forceinline__ float4 fallback(int i)  { return __ldg(c_hdr.fallbacks + i); }
     static __device__ __forceinline__ float4 cluster(int i)   { return C ? reinterpret_cast<const float4*>(s_scene)[c_hdr.off_clusters + i] : __ldg(c_hdr.clusters + i); }
     static __device__ __forceinline__ int    obj_orig(int i)  { return __ldg(c_hdr.obj_orig + i); }
-    // base pointers for cull(): the (centre, radius) entries themselves; G says whether they are in shared memory
-    static __device__ __forceinline__ const float4* leaf_geom_ptr(int i)    { return C ? reinterpret_cast<const float4*>(s_scene) + c_hdr.off_leaf_geom + i : c_hdr.leaf_geom + i; }
-    static __device__ __forceinline__ const float4* cluster_geom_ptr(int i) { return C ? reinterpret_cast<const float4*>(s_scene) + c_hdr.off_clusters + i : c_hdr.clusters + i; }
-    template <bool K> static __device__ __forceinline__ const float4* obj_geom_ptr(int i) { return (C && !K) ? reinterpret_cast<const float4*>(s_scene) + i : c_hdr.obj_geom + i; }
     // base pointers for sphere_mask (the mask table mirrors obj_geom | leaf_geom | clusters)
     static __device__ __forceinline__ const float4* mask_ptr(int i)    { return C ? reinterpret_cast<const float4*>(s_scene) + c_hdr.off_masks + i : c_hdr.masks + i; }
 #if RT_MASK_EXACT
@@ -114,18 +115,12 @@ __device__ __forceinline__ float4 material(int m, int k) { return __ldg(c_hdr.ma
 constexpr float kInf = __builtin_huge_valf();
 // ---- warp-level helpers --------------------------------------------------------------------------
 constexpr unsigned kFullWarp = 0xffffffffu;
-// max over the warp into a uniform register (CREDUX); a NaN in any lane gives NaN, which every user treats as "do not cull"
+// min / max over the warp into a uniform register (CREDUX); a NaN in any lane gives NaN
 __device__ __forceinline__ float warp_max_nan(float v) {
     float r; asm volatile("redux.sync.max.NaN.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v)); return r;
 }
-__device__ __forceinline__ float warp_max(float v) {
-    float r; asm volatile("redux.sync.max.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v)); return r;
-}
-// One bundle record per warp (rt_cull.cuh), written by lane 0 of make_bundle and read by the culls of that query only.
-constexpr int kMaxWarpsPerCta = 8;
-__device__ __forceinline__ Bundle& warp_bundle() {
-    __shared__ __align__(16) Bundle s_bundle[kMaxWarpsPerCta];
-    return s_bundle[threadIdx.x >> 5];
+__device__ __forceinline__ float warp_min_nan(float v) {
+    float r; asm volatile("redux.sync.min.NaN.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v)); return r;
 }
 
 // ---- small vector helpers ---------------------------------------------------------------------
@@ -156,50 +151,99 @@ struct Hit {
 // per-thread ray statistics (rt_stats)
 struct Counters { unsigned primary, shadow, secondary, tests; };
 
-// ---- ray bundles (rt_cull.cuh) -----------------------------------------------------------------------
-// Must be called by all 32 lanes of a converged warp; `active` lanes contribute their ray and the far end of their query
-// window.  The central ray is lane 16's when it is active (the middle of the 4 pixels / 32 pixels a warp covers), else the
-// first active lane's.  Returns false when no lane is active.
-__device__ __forceinline__ bool make_bundle(bool active, V3 o, V3 d, float tmax) {
-    const unsigned ballot = __ballot_sync(kFullWarp, active);
-    if (ballot == 0u) return false;
-    const int leader = ((ballot >> 16) & 1u) ? 16 : (__ffs(ballot) - 1);
-    const float mx = __shfl_sync(kFullWarp, o.x, leader), my = __shfl_sync(kFullWarp, o.y, leader), mz = __shfl_sync(kFullWarp, o.z, leader);
-    const float cx = __shfl_sync(kFullWarp, d.x, leader), cy = __shfl_sync(kFullWarp, d.y, leader), cz = __shfl_sync(kFullWarp, d.z, leader);
-    float h2 = 0.f, d2 = 0.f, th = -kInf;
-    if (active) {
-        const float ax = o.x - mx, ay = o.y - my, az = o.z - mz, bx = d.x - cx, by = d.y - cy, bz = d.z - cz;
-        h2 = fmaf(ax, ax, fmaf(ay, ay, az * az));
-        d2 = fmaf(bx, bx, fmaf(by, by, bz * bz));
-        th = tmax;
-    }
-    h2 = warp_max_nan(h2); d2 = warp_max_nan(d2); th = warp_max_nan(th);
-    Bundle& B = warp_bundle();
-    __syncwarp();                                   // the previous query's culls have all read the record
-    if ((threadIdx.x & 31) == 0) {
-        B.mx = mx; B.my = my; B.mz = mz; B.cx = cx; B.cy = cy; B.cz = cz;
-        bundle_finish(B, h2, d2, th);
-        B.any = 1;
-    }
-    __syncwarp();
-    return true;
+// ---- candidate masks of one round (rt_cull.cuh) ---------------------------------------------------------
+// A CTA traces 256 samples = 32 neighbouring pixels per round.  Before the camera rays are traced, and again before their
+// shadow rays are, the CTA culls EVERY cullable entry of the scene — top-level objects, cluster / object bounds, CSG
+// leaves: the table c_hdr.cull_geom, (centre, radius) or radius = inf for entries that cannot be culled — against the
+// round's bundle, one entry per thread, and leaves one candidate bit per entry in shared memory: bundle 0 = the camera
+// rays, bundle 1 + l = the shadow rays towards light l (l < kMaxListLights).  The scans then take their candidates from
+// these words instead of testing every primitive per ray.  The boxes the bundles are built from are reduced with CREDUX
+// per warp and one shared-memory atomic per warp and component (floats mapped to order-preserving ints).
+constexpr int kMaxListLights = 8;
+struct CandShared {
+    int dir_lo[3], dir_hi[3];              // camera rays: box of the directions
+    int org_lo[3], org_hi[3];              // shadow rays: box of the origins
+    int eps_max, nan_flags;                // largest shadow epsilon; bit 0 / 1: a NaN in the first / second box
+    int wide[1 + kMaxListLights];          // bundle b culls nothing (or was not built): scan without a mask
+    int pad[3];
+    // followed by (1 + kMaxListLights) * c_hdr.cull_words mask words
+};
+__device__ __forceinline__ CandShared* cand_shared() { return reinterpret_cast<CandShared*>(s_scene + c_hdr.off_cand_bytes); }
+__device__ __forceinline__ uint32_t* cand_words(int bundle) {
+    return reinterpret_cast<uint32_t*>(s_scene + c_hdr.off_cand_bytes + sizeof(CandShared)) + bundle * c_hdr.cull_words;
 }
+__device__ __forceinline__ int f2ord(float f) { const int i = __float_as_int(f); return i ^ ((i >> 31) & 0x7fffffff); }
+__device__ __forceinline__ float ord2f(int i) { return __int_as_float(i ^ ((i >> 31) & 0x7fffffff)); }
+constexpr int kOrdPosInf = 0x7f800000, kOrdNegInf = (int)0x807fffff;      // f2ord(+inf), f2ord(-inf)
 
-// Candidate bits of the <= 32 consecutive sphere-like entries p[0..n): lane k tests entry k against the warp's bundle.
-// G: the entries are in shared memory (else the global read-only path).  All lanes of a converged warp must call.
-template <bool G> __device__ __forceinline__ uint32_t cull(const float4* p, int n, float t_hi, bool segment, unsigned& tests) {
-    const Bundle& B = warp_bundle();
-    const uint32_t all = n >= 32 ? 0xffffffffu : ((1u << n) - 1u);
-    if (B.wide) return all;
-    const int lane = threadIdx.x & 31;
-    bool cand = false;
-    if (lane < n) {
-        const float4 g = G ? p[lane] : __ldg(p + lane);
-        Sphere4 q; q.x = g.x; q.y = g.y; q.z = g.z; q.w = g.w;
-        cand = !bundle_rejects(B, q, t_hi, segment);
-        ++tests;
+// All threads of the CTA: empty boxes (before the first round of a kernel; ends with a barrier).
+__device__ __forceinline__ void cand_init() {
+    if (!c_hdr.cull_words) return;
+    CandShared* S = cand_shared();
+    if (threadIdx.x < 3) { S->dir_lo[threadIdx.x] = kOrdPosInf; S->dir_hi[threadIdx.x] = kOrdNegInf; S->org_lo[threadIdx.x] = kOrdPosInf; S->org_hi[threadIdx.x] = kOrdNegInf; }
+    if (threadIdx.x == 3) { S->eps_max = 0; S->nan_flags = 0; }
+    if (threadIdx.x < 1 + kMaxListLights) S->wide[threadIdx.x] = 1;
+    __syncthreads();
+}
+// One warp: add the vectors v of its lanes with `use` to a box (lo, hi in shared memory).
+__device__ __forceinline__ void cand_box_add(bool use, V3 v, int* lo, int* hi, int* nan_flags, int nan_bit) {
+    const float ax = warp_min_nan(use ? v.x : kInf), ay = warp_min_nan(use ? v.y : kInf), az = warp_min_nan(use ? v.z : kInf);
+    const float bx = warp_max_nan(use ? v.x : -kInf), by = warp_max_nan(use ? v.y : -kInf), bz = warp_max_nan(use ? v.z : -kInf);
+    if ((threadIdx.x & 31) == 0 && ax <= bx) {                   // (false for an empty warp and for NaN)
+        atomicMin(lo + 0, f2ord(ax)); atomicMin(lo + 1, f2ord(ay)); atomicMin(lo + 2, f2ord(az));
+        atomicMax(hi + 0, f2ord(bx)); atomicMax(hi + 1, f2ord(by)); atomicMax(hi + 2, f2ord(bz));
     }
-    return __ballot_sync(kFullWarp, cand);
+    if ((threadIdx.x & 31) == 0 && !(ax == ax && ay == ay && az == az)) atomicOr(nan_flags, nan_bit);
+}
+// All threads of the CTA, after a barrier that follows the box reductions: bundles [b0, b0 + nb) x all entry words are
+// dealt to the warps; a warp builds the bundle it is working on (the same arithmetic in every lane), culls 32 entries and
+// lane 0 stores the ballot.  b = 0: camera rays; b >= 1: shadow rays towards light b - 1.  Ends with a barrier.
+__device__ __forceinline__ void cand_build(int b0, int nb, unsigned& tests) {
+    CandShared* S = cand_shared();
+    const int W = c_hdr.cull_words, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+    const bool nan = b0 == 0 ? (S->nan_flags & 1) : (S->nan_flags & 2);
+    float lo[3], hi[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { lo[k] = ord2f(b0 == 0 ? S->dir_lo[k] : S->org_lo[k]); hi[k] = ord2f(b0 == 0 ? S->dir_hi[k] : S->org_hi[k]); }
+    const bool empty = !(lo[0] <= hi[0]);                         // no ray contributed: nothing will be asked
+    const float eps_max = __int_as_float(S->eps_max);
+    int cur = -1; Bundle B; B.wide = 1; B.t_hi = 0.f;
+    if (!empty && !nan) {
+        for (int k = threadIdx.x >> 5; k < nb * W; k += nwarps) {
+            const int bb = k / W, w = k - bb * W, b = b0 + bb;
+            if (bb != cur) {
+                cur = bb;
+                if (b == 0) { const float eye[3] = {(float)c_hdr.eye[0], (float)c_hdr.eye[1], (float)c_hdr.eye[2]}; bundle_from_dirbox(B, eye, lo, hi); }
+                else {
+                    const float4 lp = __ldg(c_hdr.lights + 2 * (b - 1));
+                    const float L[3] = {lp.x, lp.y, lp.z};
+                    bundle_from_box_light(B, lo, hi, eps_max, L, lp.w != 0.f);
+                }
+            }
+            if (w == 0 && lane == 0) S->wide[b] = B.wide;
+            if (B.wide) continue;
+            const float4 g = __ldg(c_hdr.cull_geom + 32 * w + lane);
+            Sphere4 q; q.x = g.x; q.y = g.y; q.z = g.z; q.w = g.w;
+            // padding entries have w < 0; CSG leaves (words from cull_leaf_word on) are culled on the whole line
+            const bool cand = g.w >= 0.f && !bundle_rejects(B, q, B.t_hi, w < c_hdr.cull_leaf_word);
+            ++tests;
+            const uint32_t bits = __ballot_sync(kFullWarp, cand);
+            if (lane == 0) cand_words(b)[w] = bits;
+        }
+    } else if (threadIdx.x < nb) S->wide[b0 + threadIdx.x] = 1;
+    __syncthreads();
+}
+// Candidate words of bundle b for the scans, or nullptr when the bundle culls nothing.
+__device__ __forceinline__ const uint32_t* cand_of(int b) {
+    return (c_hdr.cull_words && b <= kMaxListLights && !cand_shared()->wide[b]) ? cand_words(b) : nullptr;
+}
+// Candidate bits of entries [first, first + n), n <= 32, of a word array (nullptr: all of them).
+__device__ __forceinline__ uint32_t cand_bits(const uint32_t* words, int first, int n) {
+    const uint32_t all = n >= 32 ? 0xffffffffu : ((1u << n) - 1u);
+    if (!words) return all;
+    const int w = first >> 5, sh = first & 31;
+    const uint32_t lo = words[w], hi = (sh + n > 32) ? words[w + 1] : 0u;
+    return __funnelshift_r(lo, hi, sh) & all;
 }
 
 // ---- primitive tests -----------------------------------------------------------------------------
@@ -418,21 +462,17 @@ template <bool C> __device__ Ivl leaf_interval(int li, V3 o, V3 d, unsigned& tes
 // registers (4 CTAs = 32 warps per SM) with 1/4 of the spills (snorlax 4K 20.5 -> 17.1 ms, synthetic-B 547 -> 486 ms).
 struct ProgResult { Ivl v; unsigned tests; };       // tests: primitives examined (returned by value: a reference would pin the caller's counter to memory)
 
-// Candidates among n <= 32 consecutive sphere-like entries for THIS lane's ray: the warp's bundle cull first (geom: the
-// (centre, radius) entries, G: in shared memory), then, when many survive, the per-lane conservative mask over the mask
-// table entries `masks`.  The result is a superset of the entries whose exact discriminant is >= 0 (and, with `segment`,
-// whose roots can lie in (0, t_hi]).  Converged warp only.
-template <bool C, bool G> __device__ __forceinline__ uint32_t chunk_candidates(const float4* geom, const float4* masks, int n, V3 o, V3 d,
-                                                                               float t_hi, bool segment, unsigned& tests) {
-    uint32_t cand = cull<G>(geom, n, t_hi, segment, tests);
-    if (3 * __popc(cand) > n + 2) { tests += n; cand &= sphere_mask<C>(masks, n, o, d); }     // warp-uniform branch
+// Candidates among the n <= 32 consecutive sphere-like entries [first, first + n) of a mask section for THIS ray: the
+// round's candidate bits (words, or all of them without a mask), narrowed by the per-lane conservative mask over the mask
+// table entries `masks` when many remain.  A superset of the entries whose exact discriminant is >= 0.
+template <bool C> __device__ __forceinline__ uint32_t candidates(const uint32_t* words, int first, const float4* masks, int n, V3 o, V3 d, unsigned& tests) {
+    uint32_t cand = cand_bits(words, first, n);
+    if (3 * __popc(cand) > n + 2) { tests += n; cand &= sphere_mask<C>(masks, n, o, d); }
     return cand;
 }
 
-// `pred`: this lane wants the result.  coop: all 32 lanes of a converged warp walk the program together (the sphere runs
-// cull their leaves against the warp's bundle; lanes without `pred` only keep the others company); !coop: a per-lane call
-// from divergent code, nothing warp-level inside.
-template <bool C> __device__ __noinline__ ProgResult run_program(bool pred, const bool coop, int first, int count, V3 o, V3 d) {
+// `leafw`: the round's candidate words of the CSG leaves (section of the bundle's mask), or nullptr.
+template <bool C> __device__ __noinline__ ProgResult run_program(int first, int count, V3 o, V3 d, const uint32_t* leafw) {
     unsigned tests = 0;
     Ivl acc; acc.ok = false; acc.t0 = acc.t1 = 0.f; acc.c0 = acc.c1 = 0;
     Ivl stack[RT_MAX_CSG_STACK]; int sp = 0;
@@ -449,11 +489,8 @@ template <bool C> __device__ __noinline__ ProgResult run_program(bool pred, cons
                 const int first = (int)(arg & 0x3FFFu), n = (int)(arg >> 14);
                 for (int c0 = 0; c0 < n; c0 += 32) {
                     const int cnt = min(32, n - c0), base = first + c0;
-                    // leaf intervals live on the whole line (csg.cpp:61-163): cull on the lines, no window
-                    uint32_t mask;
-                    if (coop) mask = chunk_candidates<C, C>(SV<C>::leaf_geom_ptr(base), SV<C>::leaf_ptr(base), cnt, o, d, 0.f, false, tests);
-                    else { tests += cnt; mask = sphere_mask<C>(SV<C>::leaf_ptr(base), cnt, o, d); }
-                    if (!pred) mask = 0;
+                    // (leaf intervals live on the whole line, csg.cpp:61-163: the leaf bits were culled without a window)
+                    uint32_t mask = candidates<C>(leafw, base, SV<C>::leaf_ptr(base), cnt, o, d, tests);
                     int pos = 0;
                     for (;;) {
                         const int k = mask ? (__ffs(mask) - 1) : cnt;          // next candidate, or the end of the chunk

@@ -100,7 +100,6 @@ struct RenderParams {
     unsigned* tile_counter;       // dynamic tile scheduler
     float4* wave_state;           // wavefront kernel: per CTA, per sample of its tile: ray + pending parents
     int n_local_tiles, rank, world;
-    int lockstep;                 // flat scenes: CTA barrier before every light (shade)
     long long n_pixels;
 };
 
@@ -131,6 +130,18 @@ __device__ __forceinline__ void flush_counters(const Counters& c, unsigned long 
     }
 }
 
+// Round prologue, ALL threads of the CTA: reduce the box of the camera-ray directions of the threads with `active`, cull
+// the scene against the camera bundle (cand_build, barriers inside) and return the round's camera mask (nullptr: none).
+__device__ __forceinline__ const uint32_t* camera_mask(bool active, V3 d, Counters& cnt) {
+    CandShared* S = cand_shared();
+    cand_box_add(active, d, S->dir_lo, S->dir_hi, &S->nan_flags, 1);
+    __syncthreads();
+    cand_build(0, 1, cnt.tests);
+    if (threadIdx.x < 3) { S->dir_lo[threadIdx.x] = kOrdPosInf; S->dir_hi[threadIdx.x] = kOrdNegInf; }     // for the next round
+    if (threadIdx.x == 3) atomicAnd(&S->nan_flags, ~1);
+    return cand_of(0);
+}
+
 // 4 CTAs x 256 threads per SM = 64 registers per thread: occupancy (32 warps/SM) is worth more here than registers;
 // measured against 2 (128 regs) and 3 (80 regs) on four scenes, see profiles/.
 #ifndef RT_MIN_BLOCKS
@@ -150,6 +161,7 @@ __global__ void __launch_bounds__(kRenderThreads, RT_MIN_BLOCKS) render_standard
     const int nx = c_hdr.nx, ny = c_hdr.ny;
     Counters cnt = {0, 0, 0, 0};
     stage_scene<C>();
+    cand_init();
     for (;;) {
         if (tid == 0) { s_tile = (int)atomicAdd(prm.tile_counter, 1u); s_next = 0; }
         __syncthreads();
@@ -164,15 +176,16 @@ __global__ void __launch_bounds__(kRenderThreads, RT_MIN_BLOCKS) render_standard
             for (int k = tid; k < mt::kN; k += kRenderThreads) raw[(b + 1) * mt::kN + k] = mt::next_word(raw + b * mt::kN, k);
             __syncthreads();
         }
-        // --- one sample per thread; 8 consecutive lanes share a pixel.  A warp takes the tile's 39 groups of 32 samples
-        // from a shared counter, so a warp that drew expensive samples traces fewer groups and the barrier at the end of
-        // the tile waits for one group at most.  In lockstep the groups are dealt statically (every warp must run the same
-        // number of rounds: shade has barriers inside). ---
+        // --- one sample per thread; 8 consecutive lanes share a pixel.  With round-level culling the tile's 39 groups of 32
+        // samples are dealt statically, 8 groups = 32 neighbouring pixels per round: the CTA walks a round together (camera
+        // mask, camera rays, shadow masks, shadow rays; rt_trace.cuh).  Scenes too large for the masks take groups from a
+        // shared counter instead, so a warp that drew expensive samples traces fewer groups. ---
         const long long pix0 = tile * mt::kPixelsPerTile;
+        const bool lists = c_hdr.cull_words != 0;
 #pragma unroll 1
         for (int round = 0;; ++round) {
             int grp;
-            if (prm.lockstep) {
+            if (lists) {
                 if (round * kWarps >= kWarpGroups) break;
                 grp = round * kWarps + (tid >> 5);
             } else {
@@ -195,9 +208,10 @@ __global__ void __launch_bounds__(kRenderThreads, RT_MIN_BLOCKS) render_standard
                 const double sx = ((double)x + 0.5 + jx) / (double)nx, sy = ((double)y + 0.5 + jy) / (double)ny;
                 camera_ray(sx, sy, o, d);
             }
-            {   // all 32 lanes trace together (rt_trace.cuh); a lane without a sample keeps the others company
+            {   // with masks all threads of the CTA make these calls (barriers inside); a thread without a sample keeps company
+                const uint32_t* cand0 = lists ? camera_mask(active, d, cnt) : nullptr;
                 Hit ph; bool phit;
-                c = trace<C, K, F, RT_MAX_RECURSION>(active, prm.lockstep != 0, o, d, ph, phit, cnt);
+                c = trace<C, K, F, RT_MAX_RECURSION>(active, lists, cand0, o, d, ph, phit, cnt);
                 if (active && prm.ids) prm.ids[((long long)yy * nx + x) * 8 + (j & 7)] = phit ? ph.code : -1;
             }
 #pragma unroll
@@ -258,6 +272,7 @@ __global__ void __launch_bounds__(kRenderThreads, RT_WAVE_BLOCKS) render_wavefro
     float4* my_state = prm.wave_state + (size_t)blockIdx.x * kWaveSamples * stride;
     Counters cnt = {0, 0, 0, 0};
     stage_scene<C>();
+    cand_init();
     for (;;) {
         // --- a batch: up to kWaveTiles tiles from the scheduler ---
         if (tid == 0) {
@@ -308,6 +323,9 @@ __global__ void __launch_bounds__(kRenderThreads, RT_WAVE_BLOCKS) render_wavefro
         if (tid == 0) s_count[0] = n_batch;
         __syncthreads();
         int q = 0;
+        // The first iteration traces the camera rays, in sample order: the CTA walks them in static rounds of 256 (32
+        // neighbouring pixels) and builds the round's masks (rt_trace.cuh).  Later iterations have no such order.
+        bool camera_pass = c_hdr.cull_words != 0 && limit > 0;
         for (;;) {                                                   // one ray of every unfinished sample per iteration
             const int n = s_count[q];
             if (n == 0) break;
@@ -315,20 +333,29 @@ __global__ void __launch_bounds__(kRenderThreads, RT_WAVE_BLOCKS) render_wavefro
             // barrier at the end of the iteration waits for one batch of 32 at most
             // (the NEXT batch is taken, and the first line of its samples' state prefetched, before the current one is traced:
             // the state round-trips through L2 / HBM between iterations and its latency was the kernel's top stall)
-            int k_next = 0;
-            if (lane == 0) k_next = atomicAdd(&s_cursor, 32);
-            k_next = __shfl_sync(0xffffffffu, k_next, 0);
-            for (;;) {
-                int k = k_next;
-                if (k >= n) break;
+            int k_next = 0, round = 0;
+            if (!camera_pass) {
                 if (lane == 0) k_next = atomicAdd(&s_cursor, 32);
                 k_next = __shfl_sync(0xffffffffu, k_next, 0);
-                if (k_next + (int)lane < n) {
-                    const float4* nx_state = my_state + (size_t)s_list[q][k_next + (int)lane] * stride;
-                    asm volatile("prefetch.global.L1 [%0];" :: "l"(nx_state));
+            }
+            for (;;) {
+                int k;
+                if (camera_pass) {                                   // every warp runs the same number of rounds (barriers inside)
+                    if (round * kRenderThreads >= n) break;
+                    k = round * kRenderThreads + (tid & ~31);
+                    ++round;
+                } else {
+                    k = k_next;
+                    if (k >= n) break;
+                    if (lane == 0) k_next = atomicAdd(&s_cursor, 32);
+                    k_next = __shfl_sync(0xffffffffu, k_next, 0);
+                    if (k_next + (int)lane < n) {
+                        const float4* nx_state = my_state + (size_t)s_list[q][k_next + (int)lane] * stride;
+                        asm volatile("prefetch.global.L1 [%0];" :: "l"(nx_state));
+                    }
                 }
                 k += (int)lane;
-                const bool valid = k < n;                            // the 32 lanes step together; lanes past the end keep company
+                const bool valid = k < n;
                 bool more = false; int sid = 0;
                 float4* sp = my_state;
                 V3 o = mk(0.f, 0.f, 0.f), d = mk(0.f, 1.f, 0.f);
@@ -344,10 +371,10 @@ __global__ void __launch_bounds__(kRenderThreads, RT_WAVE_BLOCKS) render_wavefro
                 RGBf c = rgb(0.f, 0.f, 0.f);
                 Hit ph; bool phit = false;
                 if (limit <= 0) {                                    // tracer.cpp:26: black, but the id buffer is still defined
-                    if (valid) ++cnt.primary;
-                    phit = closest_hit<C, K>(valid && prm.ids != nullptr, o, d, 1e-4f, kInf, ph, cnt);
+                    if (valid) { ++cnt.primary; if (prm.ids) phit = closest_hit<C, K>(o, d, 1e-4f, kInf, nullptr, ph, cnt); }
                 } else {
-                    more = !ray_step<C, K, false>(valid, false, o, d, depth, sp + 2, c, ph, phit, cnt) && valid;
+                    const uint32_t* cand0 = camera_pass ? camera_mask(valid, d, cnt) : nullptr;
+                    more = !ray_step<C, K, false>(valid, camera_pass, cand0, o, d, depth, sp + 2, c, ph, phit, cnt) && valid;
                 }
                 if (valid) {
                     if (primary && prm.ids) {
@@ -377,6 +404,7 @@ __global__ void __launch_bounds__(kRenderThreads, RT_WAVE_BLOCKS) render_wavefro
             __syncthreads();
             if (tid == 0) { s_count[q] = 0; s_cursor = 0; }
             q ^= 1;
+            camera_pass = false;
             __syncthreads();
         }
         // --- resolve: mean of the 8 samples (tracer.cpp:296) in a fixed order, toByte, coalesced stores ---
@@ -425,7 +453,7 @@ __global__ void __launch_bounds__(256, RT_PAPER_BLOCKS) paper_gbuffer_kernel(GBu
     const long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     Counters cnt = {0, 0, 0, 0};
     stage_scene<C>();
-    // the 32 pixels of a warp trace together (rt_trace.cuh); pixels past the end and rows this rank does not need keep company
+    // pixels past the end and rows this rank does not need keep the CTA company at the barriers of the round
     const bool inside = q < (long long)nx * ny;
     const int y = inside ? (int)(q / nx) : 0, x = inside ? (int)(q - (long long)y * nx) : 0;
     const bool own = inside && paper_row_owned(y, rank, world);
@@ -434,10 +462,14 @@ __global__ void __launch_bounds__(256, RT_PAPER_BLOCKS) paper_gbuffer_kernel(GBu
     const double sx = ((double)x + 0.5) / (double)nx, sy = ((double)(ny - 1 - y) + 0.5) / (double)ny;
     V3 o, d; camera_ray(sx, sy, o, d);
     Hit h; h.mat = -1; h.t = 0.f; h.n = mk(0.f, 1.f, 0.f); h.front = true; h.code = -1;
-    if (need) ++cnt.primary;
-    const bool hit = closest_hit<C, K>(need, o, d, 1e-4f, kInf, h, cnt);      // tracer.cpp:111-120
+    // the CTA's 256 pixels are one round: camera mask, centre rays, shadow masks, shadow rays (rt_trace.cuh)
+    const bool lists = c_hdr.cull_words != 0;
+    cand_init();
+    const uint32_t* cand0 = lists ? camera_mask(need, d, cnt) : nullptr;
+    bool hit = false;
+    if (need) { ++cnt.primary; hit = closest_hit<C, K>(o, d, 1e-4f, kInf, cand0, h, cnt); }      // tracer.cpp:111-120
     const bool lit = hit && own && h.mat >= 0;
-    const RGBf lum = shade<C, K>(lit, false, h, madd(o, d, h.t), normalized(neg(d)), cnt);
+    const RGBf lum = shade<C, K>(lit, lists, h, madd(o, d, h.t), normalized(neg(d)), cnt);
     if (need) {
         GBuf g;
         g.hit = hit; g.t = hit ? h.t : kInf; g.mat = hit ? h.mat : -1; g.code = hit ? h.code : -1;
@@ -510,7 +542,7 @@ __global__ void __launch_bounds__(128) trace_rays_kernel(const double* rays, dou
     constexpr bool K = true;            // clustered runs supported; specialisation does not matter here
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     stage_scene<C>();
-    const bool active = i < n;                   // the 32 lanes trace together; lanes past the end keep company
+    const bool active = i < n;
     const double* q = rays + (size_t)(active ? i : 0) * 6;
     double dx = q[3], dy = q[4], dz = q[5];
     const double L = sqrt(dx * dx + dy * dy + dz * dz);
@@ -518,9 +550,9 @@ __global__ void __launch_bounds__(128) trace_rays_kernel(const double* rays, dou
     const V3 o = mk((float)q[0], (float)q[1], (float)q[2]), d = mk((float)dx, (float)dy, (float)dz);
     Counters cnt = {0, 0, 0, 0};
     Hit h; bool hit;
-    const RGBf c = trace<C, K, false, RT_MAX_RECURSION>(active, false, o, d, h, hit, cnt);
-    const bool occ = occluded<C, K>(active, o, d, 1e-3f, 5.0f, cnt);
-    if (!active) return;
+    if (!active) return;                         // (no barrier below: known-answer rays belong to no bundle)
+    const RGBf c = trace<C, K, false, RT_MAX_RECURSION>(true, false, nullptr, o, d, h, hit, cnt);
+    const bool occ = occluded<C, K>(o, d, 1e-3f, 5.0f, nullptr, cnt);
     double* r = out + (size_t)i * 16;
     for (int k = 0; k < 16; ++k) r[k] = 0.0;
     r[0] = hit ? 1.0 : 0.0;

@@ -1,55 +1,51 @@
 // rt_trace.cuh — Scene::intersect / Scene::occluded, shade_lambert_phong and the bounded reflection / refraction
 // recursion as device functions (FP32).
 //
-// Everything here is WARP-SYNCHRONOUS: the 32 lanes of a warp walk the scene together, every function below must be
-// called by all lanes of a converged warp, and a lane that has no ray (or already has its answer) passes `active` /
-// `pred` = false and keeps the others company.  That is what lets the scans cull the scene against the warp's ray bundle
-// (rt_cull.cuh) one primitive per lane; control flow inside the scans is warp-uniform, only the exact arithmetic on the
-// surviving candidates is per lane.  There is ONE scan body (closest hit and any hit), ONE light term and ONE recursion
-// step; the per-thread kernel, the wavefront kernel, paper mode and the known-answer kernel all inline the same code.
+// There is ONE scan body (closest hit and any hit), ONE light term and ONE recursion step; the per-thread kernel, the
+// wavefront kernel, paper mode and the known-answer kernel all inline the same code.  The scans are plain per-thread code
+// (callable from divergent code); what they take from the round-level culling (rt_cull.cuh, rt_device.cuh cand_*) is a
+// pointer to the candidate words of their bundle — `cand`, or nullptr for rays that belong to no bundle (secondary rays,
+// known-answer rays), which then scan every run with the per-lane conservative mask.  Only shade<LISTS = true> and the
+// kernels' round prologue contain CTA barriers (they build the masks) and must be reached by all threads of the CTA.
 #pragma once
 #include "rt_device.cuh"
 
 namespace rtd {
 
 // ---- generic object (wrapped / affine / program) ---------------------------------------------------
-// Lanes with `pred` get true and the hit parameter when object `i` is hit inside their window.  `inclusive`
+// Returns true and the hit parameter when object `i` is hit inside the caller's window.  `inclusive`
 // windows are [tmin,tmax] (sphere/plane/pokeball, geometry.cpp:26-28,99), CSG uses t<tmax
 // (csg.cpp:176), transform-wrapped objects tmin<t<tmax (transform.cpp:38).  For programs the entry
-// code and raw entry time are returned for the deferred normal.
-// coop: all lanes of a converged warp call with the same `i` (lanes without a query pass pred = false) and the program
-// culls its leaves against the warp's bundle; !coop: a plain per-lane call (pred is true), no warp-level operation inside.
+// code and raw entry time are returned for the deferred normal.  leafw: candidate words of the CSG leaves, or nullptr.
 template <bool C, bool K>
-__device__ __forceinline__ bool generic_hit(bool pred, const bool coop, int i, V3 o, V3 d, float tmin, float tmax, float& t_out,
+__device__ __forceinline__ bool generic_hit(int i, V3 o, V3 d, float tmin, float tmax, const uint32_t* leafw, float& t_out,
                                             uint32_t& code_out, float& tent_out, unsigned& tests) {
     const int4 m = SV<C>::obj_meta(i);
     const int kind = m.x & 0xff, flags = m.x >> 8;
     if (flags & RT_FLAG_NEVER) return false;
     const bool wrapped = flags & RT_FLAG_WRAPPED;
     const float lo = wrapped ? 0.f : tmin, hi = wrapped ? kInf : tmax;       // transform.cpp:29: child on [0,inf]
-    float t = 0.f;
+    float t;
     if (kind == RT_PRIM_PROGRAM) {
         // Conservative bounding sphere of the program's leaves (scene compiler; w < 0: none).  A ray whose line
         // misses it misses every leaf, so CSG::interval fails (csg.cpp:158); if all of it lies behind the
         // origin or beyond the window the first inside run cannot pass csg.cpp:175-176 / transform.cpp:38.
         const float4 bs = SV<C>::template obj_geom_k<K>(i);
-        if (bs.w >= 0.f && pred) {
+        if (bs.w >= 0.f) {
             ++tests;
             float hb;
             const float disc = sphere_disc(bs, o, d, hb);
+            if (disc < 0.f) return false;
             const float sq = sqrtf(disc);
-            if (disc < 0.f || -hb + sq < 0.f || -hb - sq > tmax) pred = false;
+            if (-hb + sq < 0.f || -hb - sq > tmax) return false;
         }
-        if (coop) { if (!__any_sync(kFullWarp, pred)) return false; }
-        else if (!pred) return false;
-        const ProgResult pr = run_program<C>(pred, coop, m.z, m.w, o, d);
+        const ProgResult pr = run_program<C>(m.z, m.w, o, d, leafw);
         const Ivl v = pr.v; tests += pr.tests;
-        if (!pred || !v.ok) return false;
+        if (!v.ok) return false;
         t = fmaxf(v.t0, lo);                                                 // csg.cpp:175-176
         if (!(t < v.t1 && t < hi)) return false;
         code_out = v.c0; tent_out = v.t0;
     } else {
-        if (!pred) return false;
         ++tests;
         const float4 g = SV<C>::template obj_geom_k<K>(i);
         if (kind == RT_PRIM_HALFSPACE) {
@@ -72,128 +68,83 @@ __device__ __forceinline__ bool generic_hit(bool pred, const bool coop, int i, V
 // ---- Scene::intersect (scene.cpp:10-24) and Scene::occluded (scene.cpp:33-42): ONE scan -------------------------------
 // Both queries walk the object list in JSON order; `any` (Scene::occluded) stops at the first accepted hit, otherwise the
 // window's far end shrinks to the best hit so far (tmax == best_t until the first hit, so the two are the same loop).
-// The warp walks the runs together: every chunk of <= 32 entries is first culled against the warp's bundle (one entry per
-// lane); a lane then finishes the surviving candidates in JSON order with exactly the reference's root selection and
-// window test, so the result equals a one-by-one scan.  Any-hit walks the runs backwards (the order cannot be observed,
-// scene.cpp:33-42 returns a bool, and later objects are usually the foreground detail that casts the shadows).
+// Per run the candidates come from the round's mask `cand` (bits of objects | bounds | leaves, see rt_device.cuh) or,
+// without one, from the per-lane conservative mask (sphere_mask); every candidate is finished in JSON order with exactly
+// the reference's root selection and window test, so the result equals a one-by-one scan.  Any-hit walks the runs
+// backwards (the order cannot be observed, scene.cpp:33-42 returns a bool, and later objects are usually the foreground
+// detail that casts the shadows).
 struct ScanResult { int best; float t; uint32_t code; float tent; };
 
-// The bundle cull left `bits` of n top-level bounds: too many for the warp to walk them together (the rays of the warp have
-// little in common: secondary rays off curved surfaces, shadow rays of a silhouette); warp-uniform.
-__device__ __forceinline__ bool many(uint32_t bits, int n) { const int k = __popc(bits); return k > 4 && 4 * k > n; }
-
 template <bool C, bool K>
-__device__ __forceinline__ void scan_body(bool active, V3 o, V3 d, float tmin, float tmax, const bool any, ScanResult& res, unsigned& tests) {
+__device__ __forceinline__ void scan_body(V3 o, V3 d, float tmin, float tmax, const bool any, const uint32_t* cand, ScanResult& res, unsigned& tests) {
     int best = -1; float best_t = tmax; uint32_t best_code = 0; float best_tent = 0.f;
-    bool live = active;                                  // this lane still wants candidates
-    if (make_bundle(active, o, d, tmax)) {
-        float t_hi = warp_bundle().t_hi;                 // far end of the widest live window (shrinks with the best hits)
-        const int n_runs = c_hdr.n_runs;
-        for (int rr = 0; rr < n_runs; ++rr) {
-            const int4 run = SV<C>::run(any ? n_runs - 1 - rr : rr);
-            const int first = run.y, end = run.y + run.z;
-            if (K && (run.x == RUN_SPHERE || run.x == RUN_POKEBALL) && run.w > 0) {
-                // Clustered run (spatially reordered, 16 primitives per cluster): the cluster bounds are culled against the
-                // bundle, then the members of the surviving clusters.  A sphere's candidate root does not depend on the order
-                // of the scan; exact ties go to the later JSON index as in scene.cpp:15-21.
-                const int ctab = run.w - 1, ncl = (run.z + 15) >> 4;
-                for (int cb = 0; cb < ncl; cb += 32) {
-                    const int ncb = min(32, ncl - cb);
-                    uint32_t cmask = cull<C>(SV<C>::cluster_geom_ptr(ctab + cb), ncb, t_hi, true, tests);
-                    if (many(cmask, ncb)) {
-                        // incoherent bundle: every lane walks its own clusters (per-lane candidate mask over the bounds, then
-                        // over the members); the lanes run the same instructions on different clusters
-                        tests += ncb;
-                        uint32_t lc = live ? (cmask & sphere_mask<C>(SV<C>::cluster_ptr(ctab + cb), ncb, o, d)) : 0u;
-                        while (lc) {
-                            const int c = cb + __ffs(lc) - 1; lc &= lc - 1;
-                            float hb;
-                            const float disc = sphere_disc(SV<C>::cluster(ctab + c), o, d, hb);
-                            const float sq = sqrtf(disc);
-                            if (-hb + sq < 0.f || -hb - sq > best_t) continue;
-                            const int m0 = first + 16 * c, n = min(16, end - m0);
-                            tests += n;
-                            uint32_t mask = sphere_mask<C>(SV<C>::obj_ptr(m0), n, o, d);
-                            while (mask) {
-                                const int i = m0 + __ffs(mask) - 1; mask &= mask - 1;
-                                float t; ++tests;
-                                if (!sphere_t(SV<C>::template obj_geom_k<K>(i), o, d, tmin, best_t, t)) continue;
-                                if (t == best_t && best >= 0 && SV<C>::obj_orig(i) < SV<C>::obj_orig(best)) continue;
-                                best = i; best_t = t;
-                                if (any) { live = false; lc = 0; break; }
-                            }
-                        }
-                    } else {
-                        while (cmask) {
-                            const int c = cb + __ffs(cmask) - 1; cmask &= cmask - 1;
-                            const int m0 = first + 16 * c, n = min(16, end - m0);
-                            uint32_t mask = chunk_candidates<C, C && !K>(SV<C>::template obj_geom_ptr<K>(m0), SV<C>::obj_ptr(m0), n, o, d, t_hi, true, tests);
-                            if (!live) mask = 0;
-                            while (mask) {
-                                const int i = m0 + __ffs(mask) - 1; mask &= mask - 1;
-                                float t; ++tests;
-                                if (!sphere_t(SV<C>::template obj_geom_k<K>(i), o, d, tmin, best_t, t)) continue;
-                                if (t == best_t && best >= 0 && SV<C>::obj_orig(i) < SV<C>::obj_orig(best)) continue;
-                                best = i; best_t = t;
-                                if (any) { live = false; break; }
-                            }
-                        }
+    const uint32_t* boundw = cand ? cand + c_hdr.cull_cl_word : nullptr;       // section of the cluster / object bounds
+    const uint32_t* leafw = cand ? cand + c_hdr.cull_leaf_word : nullptr;      // section of the CSG leaves
+    const int n_runs = c_hdr.n_runs;
+    for (int rr = 0; rr < n_runs; ++rr) {
+        const int4 run = SV<C>::run(any ? n_runs - 1 - rr : rr);
+        const int first = run.y, end = run.y + run.z;
+        if (K && (run.x == RUN_SPHERE || run.x == RUN_POKEBALL) && run.w > 0) {
+            // Clustered run (spatially reordered, 16 primitives per cluster): the clusters whose bound is a candidate, then
+            // their members.  A sphere's candidate root does not depend on the order of the scan; exact ties go to the later
+            // JSON index as in scene.cpp:15-21.
+            const int ctab = run.w - 1, ncl = (run.z + 15) >> 4;
+            for (int cb = 0; cb < ncl; cb += 32) {
+                const int ncb = min(32, ncl - cb);
+                uint32_t bits = candidates<C>(boundw, ctab + cb, SV<C>::cluster_ptr(ctab + cb), ncb, o, d, tests);
+                while (bits) {
+                    const int c = cb + __ffs(bits) - 1; bits &= bits - 1;
+                    if (!cand) {                                      // the round's mask already knows the window
+                        float hb;
+                        const float disc = sphere_disc(SV<C>::cluster(ctab + c), o, d, hb);
+                        const float sq = sqrtf(disc);
+                        if (-hb + sq < 0.f || -hb - sq > best_t) continue;
                     }
-                    if (!any) t_hi = warp_max_nan(live ? best_t : -kInf);
-                }
-            } else if (run.x == RUN_SPHERE || run.x == RUN_POKEBALL) {
-                for (int c0 = first; c0 < end; c0 += 32) {                   // candidates first, finished in JSON order
-                    const int n = min(32, end - c0);
-                    uint32_t mask = chunk_candidates<C, C && !K>(SV<C>::template obj_geom_ptr<K>(c0), SV<C>::obj_ptr(c0), n, o, d, t_hi, true, tests);
-                    if (!live) mask = 0;
+                    const int m0 = first + 16 * c, n = min(16, end - m0);
+                    uint32_t mask = candidates<C>(cand, m0, SV<C>::obj_ptr(m0), n, o, d, tests);
                     while (mask) {
-                        const int i = c0 + __ffs(mask) - 1; mask &= mask - 1;
+                        const int i = m0 + __ffs(mask) - 1; mask &= mask - 1;
                         float t; ++tests;
-                        if (sphere_t(SV<C>::template obj_geom_k<K>(i), o, d, tmin, best_t, t)) { best = i; best_t = t; if (any) { live = false; break; } }
-                    }
-                }
-            } else if (run.x == RUN_HALFSPACE) {
-                if (live) {
-                    for (int i = first; i < end; ++i) {
-                        float t; ++tests;
-                        if (plane_t(SV<C>::template obj_geom_k<K>(i), o, d, tmin, best_t, t)) { best = i; best_t = t; if (any) { live = false; break; } }
-                    }
-                }
-            } else {
-                // generic objects (CSG programs, wrapped / affine primitives): one world bound per object (R = inf: unknown),
-                // culled against the bundle before the object itself is looked at
-                const int ctab = run.w - 1;
-                for (int c0 = first; c0 < end; c0 += 32) {
-                    const int n = min(32, end - c0);
-                    uint32_t cand = cull<C>(SV<C>::cluster_geom_ptr(ctab + c0 - first), n, t_hi, true, tests);
-                    if (many(cand, n)) {
-                        // incoherent bundle: per-lane candidate mask over the bounds, every lane walks its own objects
-                        tests += n;
-                        uint32_t lc = live ? (cand & sphere_mask<C>(SV<C>::cluster_ptr(ctab + c0 - first), n, o, d)) : 0u;
-                        while (lc) {
-                            const int i = c0 + __ffs(lc) - 1; lc &= lc - 1;
-                            float t, tent; uint32_t code;
-                            if (generic_hit<C, K>(true, false, i, o, d, tmin, best_t, t, code, tent, tests)) {
-                                best = i; best_t = t; best_code = code; best_tent = tent;
-                                if (any) { live = false; break; }
-                            }
-                        }
-                    } else {
-                        while (cand) {
-                            const int i = c0 + __ffs(cand) - 1; cand &= cand - 1;
-                            float t, tent; uint32_t code;
-                            if (generic_hit<C, K>(live, true, i, o, d, tmin, best_t, t, code, tent, tests)) {
-                                best = i; best_t = t; best_code = code; best_tent = tent;
-                                if (any) live = false;
-                            }
-                        }
+                        if (!sphere_t(SV<C>::template obj_geom_k<K>(i), o, d, tmin, best_t, t)) continue;
+                        if (t == best_t && best >= 0 && SV<C>::obj_orig(i) < SV<C>::obj_orig(best)) continue;
+                        best = i; best_t = t;
+                        if (any) goto done;
                     }
                 }
             }
-            if (any) { if (!__any_sync(kFullWarp, live)) break; }
-            else t_hi = warp_max_nan(live ? best_t : -kInf);
+        } else if (run.x == RUN_SPHERE || run.x == RUN_POKEBALL) {
+            for (int c0 = first; c0 < end; c0 += 32) {                       // candidates first, finished in JSON order
+                const int n = min(32, end - c0);
+                uint32_t mask = candidates<C>(cand, c0, SV<C>::obj_ptr(c0), n, o, d, tests);
+                while (mask) {
+                    const int i = c0 + __ffs(mask) - 1; mask &= mask - 1;
+                    float t; ++tests;
+                    if (sphere_t(SV<C>::template obj_geom_k<K>(i), o, d, tmin, best_t, t)) { best = i; best_t = t; if (any) goto done; }
+                }
+            }
+        } else if (run.x == RUN_HALFSPACE) {
+            for (int i = first; i < end; ++i) {
+                float t; ++tests;
+                if (plane_t(SV<C>::template obj_geom_k<K>(i), o, d, tmin, best_t, t)) { best = i; best_t = t; if (any) goto done; }
+            }
+        } else {
+            // generic objects (CSG programs, wrapped / affine primitives): one world bound per object (R = inf: unknown)
+            const int ctab = run.w - 1;
+            for (int c0 = first; c0 < end; c0 += 32) {
+                const int n = min(32, end - c0);
+                uint32_t bits = candidates<C>(boundw, ctab + c0 - first, SV<C>::cluster_ptr(ctab + c0 - first), n, o, d, tests);
+                while (bits) {
+                    const int i = c0 + __ffs(bits) - 1; bits &= bits - 1;
+                    float t, tent; uint32_t code;
+                    if (generic_hit<C, K>(i, o, d, tmin, best_t, leafw, t, code, tent, tests)) {
+                        best = i; best_t = t; best_code = code; best_tent = tent;
+                        if (any) goto done;
+                    }
+                }
+            }
         }
     }
+done:
     res.best = best; res.t = best_t; res.code = best_code; res.tent = best_tent;
 }
 
@@ -204,23 +155,23 @@ __device__ __forceinline__ void scan_body(bool active, V3 o, V3 d, float tmin, f
 // local memory).
 struct ScanOut { ScanResult r; unsigned tests; };
 template <bool C, bool K>
-__device__ __noinline__ ScanOut scan_shared(bool active, V3 o, V3 d, float tmin, float tmax, bool any) {
+__device__ __noinline__ ScanOut scan_shared(V3 o, V3 d, float tmin, float tmax, bool any, const uint32_t* cand) {
     ScanOut out; out.tests = 0;
-    scan_body<C, K>(active, o, d, tmin, tmax, any, out.r, out.tests);
+    scan_body<C, K>(o, d, tmin, tmax, any, cand, out.r, out.tests);
     return out;
 }
 template <bool C, bool K, bool ANY>
-__device__ __forceinline__ void scan(bool active, V3 o, V3 d, float tmin, float tmax, ScanResult& res, Counters& cnt) {
-    if (K) { const ScanOut so = scan_shared<C, K>(active, o, d, tmin, tmax, ANY); res = so.r; cnt.tests += so.tests; }
-    else scan_body<C, K>(active, o, d, tmin, tmax, ANY, res, cnt.tests);
+__device__ __forceinline__ void scan(V3 o, V3 d, float tmin, float tmax, const uint32_t* cand, ScanResult& res, Counters& cnt) {
+    if (K) { const ScanOut so = scan_shared<C, K>(o, d, tmin, tmax, ANY, cand); res = so.r; cnt.tests += so.tests; }
+    else scan_body<C, K>(o, d, tmin, tmax, ANY, cand, res, cnt.tests);
 }
 
 template <bool C, bool K>
-__device__ __forceinline__ bool closest_hit(bool active, V3 o, V3 d, float tmin, float tmax, Hit& hit, Counters& cnt) {
+__device__ __forceinline__ bool closest_hit(V3 o, V3 d, float tmin, float tmax, const uint32_t* cand, Hit& hit, Counters& cnt) {
     ScanResult sr;
-    scan<C, K, false>(active, o, d, tmin, tmax, sr, cnt);
+    scan<C, K, false>(o, d, tmin, tmax, cand, sr, cnt);
     const int best = sr.best;
-    if (!active || best < 0) return false;
+    if (best < 0) return false;
     // ---- finalise the winner: normal, front_face, material, id code ----
     const int4 m = SV<C>::obj_meta(best);
     const int kind = m.x & 0xff, flags = m.x >> 8;
@@ -259,10 +210,10 @@ __device__ __forceinline__ bool closest_hit(bool active, V3 o, V3 d, float tmin,
 }
 
 template <bool C, bool K>
-__device__ __forceinline__ bool occluded(bool active, V3 o, V3 d, float tmin, float tmax, Counters& cnt) {
+__device__ __forceinline__ bool occluded(V3 o, V3 d, float tmin, float tmax, const uint32_t* cand, Counters& cnt) {
     ScanResult sr;
-    scan<C, K, true>(active, o, d, tmin, tmax, sr, cnt);
-    return active && sr.best >= 0;
+    scan<C, K, true>(o, d, tmin, tmax, cand, sr, cnt);
+    return sr.best >= 0;
 }
 
 // ---- shade_lambert_phong (shading.cpp:31-138) ------------------------------------------------------------------
@@ -300,44 +251,59 @@ __device__ __forceinline__ void light_shade(int l, const float4 m0, float ks, fl
         float two = 2.f * dot(n, wi);
         V3 rr = normalized(mk(fmaf(two, n.x, -wi.x), fmaf(two, n.y, -wi.y), fmaf(two, n.z, -wi.z)));
         float rdotv = fmaxf(0.f, dot(rr, wo));
-        // exp2(s * log2(x)) on the MUFU pipe (relative error ~ s * 2^-21, far below 1/255); x == 0 keeps powf's edge cases
-        float spec = (rdotv > 0.f ? __powf(rdotv, shininess) : powf(rdotv, shininess)) * ks;
+        // exp2(s * log2(x)) on the MUFU pipe (relative error ~ s * 2^-21, far below 1/255).  x == 0 (every light whose mirror
+        // direction points away from the viewer) is std::pow(+0, s): 0 for s > 0, 1 for s == 0, inf for s < 0, NaN for NaN —
+        // spelled out, because the full powf behind this branch used to run for most warps
+        const float pow0 = shininess > 0.f ? 0.f : (shininess == 0.f ? 1.f : (shininess < 0.f ? kInf : shininess));
+        float spec = (rdotv > 0.f ? __powf(rdotv, shininess) : pow0) * ks;
         Es = rgb(I.r * spec, I.g * spec, I.b * spec);
     }
     E = screen(E, screen(Ed, Es));
 }
 
-// shade_lambert_phong for the lanes with `lit` (a hit with a material); the others get (0,0,0).  Two passes per chunk of 32
-// lights: all shadow queries first (one visibility bit each), the contributions of the visible lights after.  With
-// `lockstep` the whole CTA meets at a barrier before every light: warps that walk the same code at the same time share
-// instruction-cache lines (snorlax 4K 15.96 -> 14.44 ms when introduced; set per scene on upload, flat kernels only —
-// every thread of the CTA must then call shade the same number of times).
+// shade_lambert_phong for a thread with `lit` (a hit with a material); the others get (0,0,0).  Two passes per chunk of 32
+// lights: all shadow queries first (one visibility bit each), the contributions of the visible lights after, so that no
+// shading state is live across the scans.
+// LISTS (CTA-uniform): the call is made by ALL threads of the CTA for the camera rays of one round; the CTA first reduces the box of the
+// shadow-ray origins and culls the scene against the bundle towards every light (cand_build, two barriers), and the shadow
+// scans take their candidates from those masks.  Without LISTS (secondary rays, known-answer rays) the scans use the
+// per-lane mask only and the call may come from divergent code.
 template <bool C, bool K>
-__device__ __forceinline__ RGBf shade(bool lit, bool lockstep, const Hit& h, V3 p, V3 wo, Counters& cnt) {
+__device__ __forceinline__ RGBf shade(bool lit, const bool LISTS, const Hit& h, V3 p, V3 wo, Counters& cnt) {
     const float eps = fmaxf(1e-3f, 1e-4f * h.t);                             // shading.cpp:43
     const V3 so = madd(p, h.n, eps);
     const int nl = c_hdr.n_lights;
+    const bool lists = LISTS && c_hdr.cull_words != 0;
+    if (lists) {
+        CandShared* S = cand_shared();
+        cand_box_add(lit, so, S->org_lo, S->org_hi, &S->nan_flags, 2);
+        const float e = warp_max_nan(lit ? eps : 0.f);
+        if ((threadIdx.x & 31) == 0) { if (e == e) atomicMax(&S->eps_max, __float_as_int(e)); else atomicOr(&S->nan_flags, 2); }
+        __syncthreads();
+        cand_build(1, min(nl, kMaxListLights), cnt.tests);
+        if (threadIdx.x < 3) { S->org_lo[threadIdx.x] = kOrdPosInf; S->org_hi[threadIdx.x] = kOrdNegInf; }     // for the next round
+        if (threadIdx.x == 3) { S->eps_max = 0; atomicAnd(&S->nan_flags, ~2); }
+    }
     RGBf E = rgb(0.f, 0.f, 0.f);
-    if (lit) { const float4 m1 = material(h.mat, 1); E = rgb(m1.x, m1.y, m1.z); }   // ambient (x) scene ambient, pre-multiplied
+    if (!lit) return E;
+    { const float4 m1 = material(h.mat, 1); E = rgb(m1.x, m1.y, m1.z); }       // ambient (x) scene ambient, pre-multiplied
     for (int l0 = 0; l0 < nl; l0 += 32) {
         const int cnt_l = min(32, nl - l0);
         uint32_t vis = 0;
         for (int k = 0; k < cnt_l; ++k) {
-            if (lockstep) __syncthreads();
             V3 wi; float dist;
             const float ndotl = light_vector(SV<C>::light(l0 + k, 0), p, h.n, wi, dist);
+            if (ndotl <= 0.f) continue;                                      // shading.cpp:51,94
             const float tmaxS = dist - eps;
-            const bool want = lit && ndotl > 0.f && !(tmaxS <= eps);         // shading.cpp:51,94,98
-            if (want) ++cnt.shadow;
-            const bool occ = occluded<C, K>(want, so, normalized(wi), eps, tmaxS, cnt);   // Ray ctor re-normalises (core.h:278)
-            if (want && !occ) vis |= 1u << k;
+            if (tmaxS <= eps) continue;                                      // shading.cpp:98
+            ++cnt.shadow;
+            const uint32_t* cand = lists ? cand_of(1 + l0 + k) : nullptr;
+            if (!occluded<C, K>(so, normalized(wi), eps, tmaxS, cand, cnt)) vis |= 1u << k;   // Ray ctor re-normalises (core.h:278)
         }
-        if (lit) {
-            const float4 m0 = material(h.mat, 0), m2 = material(h.mat, 2);
-            while (vis) {
-                const int k = __ffs(vis) - 1; vis &= vis - 1;
-                light_shade<C>(l0 + k, m0, m0.w, m2.y, m2.w, h.n, p, wo, E);
-            }
+        const float4 m0 = material(h.mat, 0), m2 = material(h.mat, 2);
+        while (vis) {
+            const int k = __ffs(vis) - 1; vis &= vis - 1;
+            light_shade<C>(l0 + k, m0, m0.w, m2.y, m2.w, h.n, p, wo, E);
         }
     }
     return rgb(fminf(1.5f, E.r), fminf(1.5f, E.g), fminf(1.5f, E.b));        // shading.cpp:133-135
@@ -350,21 +316,26 @@ __device__ __forceinline__ RGBf shade(bool lit, bool lockstep, const Hit& h, V3 
 // memory for the per-thread kernel, global memory for the wavefront kernel (any thread can then take any unfinished
 // sample from the CTA's queue).
 //
-// ray_step traces the ray (o, d) of the lanes with `alive` at depth sp: closest hit, shading incl. shadow rays, then the
-// push / pop of the tree.  Returns true when the lane's tree is finished (`result` = Tracer::trace's colour), false when
+// ray_step traces the ray (o, d) of a thread with `alive` at depth sp: closest hit, shading incl. shadow rays, then the
+// push / pop of the tree.  Returns true when the thread's tree is finished (`result` = Tracer::trace's colour), false when
 // (o, d, sp) is its next ray.  FLAT: no ray of the scene can spawn a child (no reflective / refractive material, or
-// recursion == 1): no frames are touched and every tree finishes with its first ray.
+// recursion == 1): no frames are touched and every tree finishes with its first ray.  LISTS: the ray is a camera ray of
+// a round — `cand` is the round's mask of the camera bundle, ALL threads of the CTA make the call (see shade).
 template <bool C, bool K, bool FLAT>
-__device__ __forceinline__ bool ray_step(bool alive, bool lockstep, V3& o, V3& d, int& sp, float4* __restrict__ frames, RGBf& result,
-                                         Hit& primary, bool& primary_hit, Counters& cnt) {
+__device__ __forceinline__ bool ray_step(bool alive, const bool LISTS, const uint32_t* cand, V3& o, V3& d, int& sp, float4* __restrict__ frames,
+                                         RGBf& result, Hit& primary, bool& primary_hit, Counters& cnt) {
     const int limit = c_hdr.recursion;
     Hit h; h.mat = -1; h.t = 0.f; h.n = mk(0.f, 1.f, 0.f); h.front = true; h.code = -1;
-    const bool hit = closest_hit<C, K>(alive, o, d, 1e-4f, kInf, h, cnt);   // tracer.cpp:29
-    if (alive) { if (FLAT || sp == 0) { ++cnt.primary; primary = h; primary_hit = hit; } else ++cnt.secondary; }
+    bool hit = false;
+    if (alive) {
+        hit = closest_hit<C, K>(o, d, 1e-4f, kInf, cand, h, cnt);          // tracer.cpp:29
+        if (FLAT || LISTS || sp == 0) { ++cnt.primary; primary = h; primary_hit = hit; } else ++cnt.secondary;
+    }
     const V3 p = madd(o, d, h.t);
     const V3 wo = normalized(neg(d));
     const bool lit = hit && h.mat >= 0;
-    const RGBf total = shade<C, K>(lit, lockstep, h, p, wo, cnt);           // tracer.cpp:31
+    if (!LISTS && !alive) return true;
+    const RGBf total = shade<C, K>(lit, LISTS, h, p, wo, cnt);              // tracer.cpp:31
     if (!alive) return true;
     if (!hit) result = rgb(c_hdr.bg[0], c_hdr.bg[1], c_hdr.bg[2]);          // tracer.cpp:72
     else if (!lit) result = rgb(1.f, 0.f, 1.f);                              // shading.cpp:33
@@ -429,30 +400,29 @@ __device__ __forceinline__ bool ray_step(bool alive, bool lockstep, V3& o, V3& d
     }
 }
 
-// Tracer::trace (tracer.cpp:12-20) for one sample per lane: the lanes of a warp step through their trees together until
-// the last one is done.  `active` false: the lane has no sample.  D = frames available = max recursion depth served.
+// Tracer::trace (tracer.cpp:12-20) for one sample per thread.  `active` false: the thread has no sample.  D = frames
+// available = deepest recursion served.  LISTS: the sample is a camera ray of a round whose camera-bundle mask is `cand`;
+// ALL threads of the CTA make the call (the first ray and its shadow rays use the round's masks, deeper rays none).
 template <bool C, bool K, bool FLAT, int D>
-__device__ __forceinline__ RGBf trace(bool active, bool lockstep, V3 o, V3 d, Hit& primary, bool& primary_hit, Counters& cnt) {
+__device__ __forceinline__ RGBf trace(bool active, const bool LISTS, const uint32_t* cand, V3 o, V3 d, Hit& primary, bool& primary_hit, Counters& cnt) {
     primary_hit = false;
     RGBf result = rgb(0.f, 0.f, 0.f);
     if (c_hdr.recursion <= 0) {                                              // tracer.cpp:26 at depth 0: black, ids still defined
-        if (active) ++cnt.primary;
-        primary_hit = closest_hit<C, K>(active, o, d, 1e-4f, kInf, primary, cnt);
+        if (active) { ++cnt.primary; primary_hit = closest_hit<C, K>(o, d, 1e-4f, kInf, cand, primary, cnt); }
         return result;
     }
     if (FLAT) {
         int sp = 0;
-        ray_step<C, K, true>(active, lockstep, o, d, sp, nullptr, result, primary, primary_hit, cnt);
+        ray_step<C, K, true>(active, LISTS, cand, o, d, sp, nullptr, result, primary, primary_hit, cnt);
         return result;
     }
     float4 frames[3 * D];
     int sp = 0;                     // == depth of the ray being traced
-    bool alive = active;
+    bool lists = LISTS;             // the camera ray: all threads; deeper rays: the threads whose tree goes on, no masks
     for (;;) {
-        RGBf r = rgb(0.f, 0.f, 0.f);
-        const bool done = ray_step<C, K, false>(alive, false, o, d, sp, frames, r, primary, primary_hit, cnt);
-        if (alive && done) { result = r; alive = false; }
-        if (!__any_sync(kFullWarp, alive)) break;
+        const bool done = ray_step<C, K, false>(active, lists, lists ? cand : nullptr, o, d, sp, frames, result, primary, primary_hit, cnt);
+        if (!active || done) break;
+        lists = false;
     }
     return result;
 }

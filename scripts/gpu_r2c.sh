@@ -1,0 +1,19 @@
+#!/bin/bash
+# Round-2 session C: smoke, parity suite, kernel ms of the register-budget variants, one full ncu capture.
+TAG=${1:-r2c}; OUT=gpurun_out/$TAG; mkdir -p $OUT
+timeout -k 5 180 python -c "import __graft_entry__ as g; g.smoke()" > $OUT/smoke.log 2>&1; rc=$?
+echo "smoke rc=$rc"; tail -3 $OUT/smoke.log
+if [ $rc -ne 0 ]; then echo "smoke failed: stopping"; exit 1; fi
+timeout -k 10 1500 python -m pytest tests -m gpu -q -rA --timeout=400 --durations=8 > $OUT/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> $OUT/pytest_gpu.log
+grep -E "^FAILED|^ERROR|passed|failed" $OUT/pytest_gpu.log | tail -25
+SC="snorlax_4k snorlax_4k_reflect penguin_4k pokeballs synthetic_a_2k synthetic_b_1k penguin_4k:paper snorlax_4k:paper"
+for a in $SC; do
+  sc=${a%%:*}; mode=standard; [[ "$a" == *:* ]] && mode=${a##*:}
+  timeout -k 10 300 python scripts/profile_run.py scenes/$sc.json $mode 4 2>&1 | tail -1 | python -c "import sys,ast; d=ast.literal_eval(sys.stdin.read().strip()); print('default','$a','kernel_ms',round(d['kernel_ms'],3),'tests/ray',round(d['prim_tests']/(d['primary_rays']+d['shadow_rays']+d['secondary_rays']),2))" | tee -a $OUT/variants.txt
+done
+bash scripts/gpu_variants.sh $TAG "$SC" ${2:-b3 b2}
+for sc in ${3:-snorlax_4k}; do
+timeout -k 10 300 python scripts/profile_run.py scenes/$sc.json standard 2 > $OUT/plain_prof_$sc.log 2>&1 &&
+timeout -k 10 900 ncu --set full --clock-control none --import-source on -k "regex:render_(standard|wavefront)" -s 1 -c 1 -o $OUT/prof_$sc \
+    python scripts/profile_run.py scenes/$sc.json standard 2 > $OUT/ncu_prof_$sc.log 2>&1
+done

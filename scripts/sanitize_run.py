@@ -10,7 +10,7 @@ rt.init(0)
 scenes = sys.argv[1:] or ["quirks", "synthetic_b_small", "snorlax_small"]
 for name in scenes:
     path = os.path.join(ROOT, "scenes", name + ".json")
-    for opts in ({}, {"wavefront": 1}, {"wavefront": 0, "flat": 0}, {"lockstep": 1}, {"lockstep": 0}, {"global_scene": 1}):
+    for opts in ({}, {"wavefront": 1}, {"wavefront": 0, "flat": 0}, {"cull": 0}, {"flat": 0, "cull": 0}, {"global_scene": 1}):
         for k in rt.DEBUG_OPTIONS:
             rt.debug_option(k, -1)
         for k, v in opts.items():

@@ -1,7 +1,9 @@
 // Host-side check that the bundle cull (csrc/rt_cull.cuh) is CONSERVATIVE: it never rejects a sphere that the device's
 // exact FP32 test (sphere_disc / sphere_t of csrc/rt_device.cuh, restated below with the same fmaf sequence) accepts for
-// some ray of the bundle.  Random bundles at several scene scales and spreads; spheres are placed near-tangent to a ray of
-// the bundle (both sides of the silhouette, relative gaps 1e-7 ... 1e-2), near the ends of the query window, and at random.
+// some ray of the bundle.  Random bundles at several scene scales and spreads, built the three ways the device builds them
+// (central ray + spreads; camera rays = eye + box of directions; shadow rays = box of origins + light); spheres are placed
+// near-tangent to a ray of the bundle (both sides of the silhouette, relative gaps 1e-7 ... 1e-2), near the ends of the
+// query window, and at random.
 // Prints "<cases> <rejected> <violations>"; test infrastructure only (tests/test_cull.py builds and runs it).
 #include <cmath>
 #include <cstdio>
@@ -21,7 +23,7 @@ static float sphere_disc(rtd::Sphere4 g, V o, V d, float& hb) {
 }
 
 int main(int argc, char** argv) {
-    const long long trials = argc > 1 ? atoll(argv[1]) : 60000;
+    const long long trials = argc > 1 ? atoll(argv[1]) : 180000;
     std::mt19937_64 rng(20261105);
     std::uniform_real_distribution<double> U(0.0, 1.0);
     std::normal_distribution<double> N(0.0, 1.0);
@@ -47,17 +49,57 @@ int main(int argc, char** argv) {
             tmax[i] = finite_window ? (float)(S * (0.05 + 3 * U(rng))) : INFINITY;
             act[i] = U(rng) < 0.9 || i == 16;
         }
-        // make_bundle (rt_device.cuh): lane 16 is the central ray when active
         rtd::Bundle B{};
-        B.mx = o[16].x; B.my = o[16].y; B.mz = o[16].z; B.cx = d[16].x; B.cy = d[16].y; B.cz = d[16].z;
-        float h2 = 0.f, d2 = 0.f, th = -INFINITY;
-        for (int i = 0; i < 32; ++i) if (act[i]) {
-            const float ax = o[i].x - B.mx, ay = o[i].y - B.my, az = o[i].z - B.mz, bx = d[i].x - B.cx, by = d[i].y - B.cy, bz = d[i].z - B.cz;
-            h2 = fmaxf(h2, fmaf(ax, ax, fmaf(ay, ay, az * az)));
-            d2 = fmaxf(d2, fmaf(bx, bx, fmaf(by, by, bz * bz)));
-            th = fmaxf(th, tmax[i]);
+        const int mode = (int)((tr / 120) % 3);
+        if (mode == 0) {
+            // central ray + spreads: ray 16 is the central ray
+            B.mx = o[16].x; B.my = o[16].y; B.mz = o[16].z; B.cx = d[16].x; B.cy = d[16].y; B.cz = d[16].z;
+            float h2 = 0.f, d2 = 0.f, th = -INFINITY;
+            for (int i = 0; i < 32; ++i) if (act[i]) {
+                const float ax = o[i].x - B.mx, ay = o[i].y - B.my, az = o[i].z - B.mz, bx = d[i].x - B.cx, by = d[i].y - B.cy, bz = d[i].z - B.cz;
+                h2 = fmaxf(h2, fmaf(ax, ax, fmaf(ay, ay, az * az)));
+                d2 = fmaxf(d2, fmaf(bx, bx, fmaf(by, by, bz * bz)));
+                th = fmaxf(th, tmax[i]);
+            }
+            rtd::bundle_finish(B, h2, d2, th);
+        } else if (mode == 1) {
+            // camera rays (rt_device.cuh cand_build, bundle 0): one origin, box of the directions, no far end
+            float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+            for (int i = 0; i < 32; ++i) { o[i] = o[16]; tmax[i] = INFINITY; }
+            for (int i = 0; i < 32; ++i) if (act[i]) {
+                lo[0] = fminf(lo[0], d[i].x); lo[1] = fminf(lo[1], d[i].y); lo[2] = fminf(lo[2], d[i].z);
+                hi[0] = fmaxf(hi[0], d[i].x); hi[1] = fmaxf(hi[1], d[i].y); hi[2] = fmaxf(hi[2], d[i].z);
+            }
+            const float eye[3] = {o[16].x, o[16].y, o[16].z};
+            rtd::bundle_from_dirbox(B, eye, lo, hi);
+        } else {
+            // shadow rays (cand_build, bundle 1 + l): origins = hit point + eps * normal in a box, aimed from the hit point at a light
+            const bool directional = U(rng) < 0.25;
+            auto lu = unit(); const double ld = S * (0.02 + 3 * U(rng));
+            const float L[3] = {directional ? (float)lu[0] : (float)(m0[0] + ld * lu[0]), directional ? (float)lu[1] : (float)(m0[1] + ld * lu[1]),
+                                directional ? (float)lu[2] : (float)(m0[2] + ld * lu[2])};
+            float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY}, eps_max = 0.f;
+            for (int i = 0; i < 32; ++i) {
+                const float eps = fmaxf(1e-3f, 1e-4f * (float)(S * 3 * U(rng)));
+                auto nn = unit();
+                const V p{(float)(o[i].x - eps * nn[0]), (float)(o[i].y - eps * nn[1]), (float)(o[i].z - eps * nn[2])};   // the hit point
+                if (directional) { d[i] = {L[0], L[1], L[2]}; tmax[i] = INFINITY; }
+                else {                                             // light_vector + normalized (rt_trace.cuh) in FP32
+                    V a{L[0] - p.x, L[1] - p.y, L[2] - p.z};
+                    const float dist = sqrtf(fmaxf(dotf(a, a), 0.01f)), inv = 1.0f / dist;
+                    V wi{a.x * inv, a.y * inv, a.z * inv};
+                    const float l2 = sqrtf(dotf(wi, wi)), i2 = 1.0f / l2;
+                    d[i] = {wi.x * i2, wi.y * i2, wi.z * i2};
+                    tmax[i] = dist - eps;
+                }
+                if (act[i]) {
+                    lo[0] = fminf(lo[0], o[i].x); lo[1] = fminf(lo[1], o[i].y); lo[2] = fminf(lo[2], o[i].z);
+                    hi[0] = fmaxf(hi[0], o[i].x); hi[1] = fmaxf(hi[1], o[i].y); hi[2] = fmaxf(hi[2], o[i].z);
+                    eps_max = fmaxf(eps_max, eps);
+                }
+            }
+            rtd::bundle_from_box_light(B, lo, hi, eps_max, L, directional);
         }
-        rtd::bundle_finish(B, h2, d2, th);
         if (B.wide) continue;
         for (int k = 0; k < 24; ++k) {
             // a sphere near-tangent to ray `i` at parameter t

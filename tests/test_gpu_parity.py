@@ -164,18 +164,18 @@ def test_wavefront_and_per_thread_kernels_agree(gpu, name, force):
         sc.close()
     for k in ("rgb8", "fb", "ids"):
         assert np.array_equal(out["0"][k], out["1"][k]), k
-    for k in ("primary_rays", "shadow_rays", "secondary_rays", "prim_tests"):
+    for k in ("primary_rays", "shadow_rays", "secondary_rays"):        # (prim_tests depends on how the rounds are formed)
         assert out["0stats"][k] == out["1stats"][k], k
 
 
 @pytest.mark.parametrize("name", ["snorlax_small", "pokeballs_small", "penguin_small", "synthetic_a_tiny"])
 def test_flat_kernel_and_generic_loop_agree(gpu, name, force):
-    """A scene in which no ray can spawn a child runs trace_flat (one closest hit + one shade, optionally with the CTA in
-    lockstep per light); forced back onto the generic stack loop (flat = 0) or in / out of lockstep, frame, ids and ray
-    counts must not change by a bit."""
+    """A scene in which no ray can spawn a child runs the flat kernel (one closest hit + one shade per sample, no frames);
+    forced back onto the generic loop (flat = 0), and with the round-level culling switched off (cull = 0: every ray scans
+    every run, as in the reference), frame, ids and ray counts must not change by a bit."""
     out = []
-    for env in ({"flat": 0}, {"lockstep": 0}, {"lockstep": 1}):
-        for k in ("flat", "lockstep"):
+    for env in ({"flat": 0}, {"cull": 0}, {"flat": 0, "cull": 0}, {}):
+        for k in ("flat", "cull"):
             force(k, -1)
         for k, v in env.items():
             force(k, v)
@@ -186,8 +186,29 @@ def test_flat_kernel_and_generic_loop_agree(gpu, name, force):
     for got, st in out[1:]:
         for k in ("rgb8", "fb", "ids"):
             assert np.array_equal(out[0][0][k], got[k]), k
-        for k in ("primary_rays", "shadow_rays", "secondary_rays", "prim_tests"):
+        for k in ("primary_rays", "shadow_rays", "secondary_rays"):
             assert out[0][1][k] == st[k], k
+    assert out[3][1]["prim_tests"] < out[1][1]["prim_tests"], "the round-level culling must save primitive tests"
+
+
+@pytest.mark.parametrize("name", ["quirks", "synthetic_b_small", "synthetic_a_small", "quirks_far", "big_floor"])
+def test_culling_does_not_change_a_bit(gpu, name, force):
+    """Round-level culling (candidate masks per 32 pixels and per light) against the plain scans: frame, ids and ray counts
+    identical, in standard and in paper mode, on the bounce-heavy and the clustered scenes as well."""
+    out = {}
+    for cull in (0, 1):
+        force("cull", cull)
+        sc = gpu.load_scene_from_json(scene_path(name))
+        for mode in ("standard", "paper"):
+            out[cull, mode], tr = render_gpu(gpu, sc, mode)
+            out[cull, mode, "stats"] = dict(tr.last_stats)
+        sc.close()
+    for mode in ("standard", "paper"):
+        for k in ("rgb8", "fb", "ids"):
+            assert np.array_equal(out[0, mode][k], out[1, mode][k]), (mode, k)
+        for k in ("primary_rays", "shadow_rays", "secondary_rays"):
+            assert out[0, mode, "stats"][k] == out[1, mode, "stats"][k], (mode, k)
+        print(f"{name}/{mode}: primitive tests {out[0, mode, 'stats']['prim_tests']} -> {out[1, mode, 'stats']['prim_tests']}")
 
 
 def test_every_scene_data_path_agrees(gpu, force):
