@@ -62,7 +62,9 @@ struct rt_scene {
     bool clustered{false};    // a long run of plain spheres / pokeballs was reordered into spatial clusters (kernel variant K)
     size_t smem_bytes{0};
     std::vector<float4> obj_geom, leaf_geom, pokeballs, affines, materials, lights, fallbacks, clusters, masks, cull_geom;
-    int cull_words{0}, cull_cl_word{0}, cull_leaf_word{0};
+    std::vector<uint32_t> cull_plane_bits;
+    int cull_words{0}, cull_leaf_word{0};
+    uint32_t* d_cull_plane_bits{nullptr};
     float mask_scale{0.f};
     std::vector<int4> obj_meta, leaf_meta, runs;
     std::vector<int> obj_orig;
@@ -242,21 +244,30 @@ void build_host_arrays(const rt_scene_desc& d, rt_scene& s) {
     for (size_t i = 0; i < s.leaf_geom.size(); ++i) add(s.leaf_geom[i], sphere_like(s.leaf_meta[i]));
     for (const float4& g : s.clusters) add(g, true);
     s.mask_scale = (float)std::min(scale * (1.0 + 1e-6), 3.0e38);
-    // Round-level culling table (rt_cull.cuh, rt_device.cuh cand_build): (centre, radius) of every top-level object, every
-    // bound (cluster of a clustered run / world bound of a generic object) and every CSG leaf, radius = inf where nothing can
-    // be said (half-spaces, affine primitives, programs without a bound: always candidates); each section padded to a multiple
-    // of 32 entries with w < 0 (never candidates).  Members of generic runs are represented by their bound, so their object
-    // entry is inf as well (the scans never ask for it).
+    // Round-level culling table (rt_cull.cuh, rt_device.cuh cand_build): one entry per top-level object (device order) and
+    // per CSG leaf: (centre, radius) of a plain sphere / pokeball; the world bound of a generic object (CSG program, wrapped
+    // primitive; the run's bound table); (n, n.p0) of a plain half-space, flagged in cull_plane_bits; radius = inf where
+    // nothing can be said (always a candidate).  Both sections are padded to a multiple of 32 entries with w < 0 (never).
     const float inf = std::numeric_limits<float>::infinity();
     auto pad32 = [&]() { while (s.cull_geom.size() % 32) s.cull_geom.push_back(make_float4(0.f, 0.f, 0.f, -1.f)); };
     auto finite4 = [](const float4& g) { return std::isfinite(g.x) && std::isfinite(g.y) && std::isfinite(g.z) && std::isfinite(g.w); };
+    std::vector<int> bound_of_obj(s.obj_geom.size(), -1);          // generic objects: index of their bound in s.clusters
+    for (const int4& r : s.runs) if (r.x == rtd::RUN_GENERIC && r.w > 0) for (int k = 0; k < r.z; ++k) bound_of_obj[(size_t)(r.y + k)] = r.w - 1 + k;
+    std::vector<size_t> planes;
     for (size_t i = 0; i < s.obj_geom.size(); ++i) {
         const float4 g = s.obj_geom[i]; const int4 m = s.obj_meta[i];
-        const bool plain = (m.x >> 8) == 0 && ((m.x & 0xff) == RT_PRIM_SPHERE || (m.x & 0xff) == RT_PRIM_POKEBALL) && finite4(g);
-        s.cull_geom.push_back(plain ? make_float4(g.x, g.y, g.z, std::fabs(g.w)) : make_float4(0.f, 0.f, 0.f, inf));
+        const int kind = m.x & 0xff, flags = m.x >> 8;
+        float4 e = make_float4(0.f, 0.f, 0.f, inf);
+        if (flags == 0 && (kind == RT_PRIM_SPHERE || kind == RT_PRIM_POKEBALL)) { if (finite4(g)) e = make_float4(g.x, g.y, g.z, std::fabs(g.w)); }
+        else if (flags == 0 && kind == RT_PRIM_HALFSPACE) {
+            const double nn = (double)g.x * g.x + (double)g.y * g.y + (double)g.z * g.z;
+            if (finite4(g) && std::fabs(nn - 1.0) < 1e-5) { e = g; planes.push_back(i); }      // the plane cull assumes a unit normal
+        } else if (bound_of_obj[i] >= 0) {
+            const float4 b = s.clusters[(size_t)bound_of_obj[i]];
+            if (finite4(b) && b.w >= 0.f) e = b;
+        }
+        s.cull_geom.push_back(e);
     }
-    pad32(); s.cull_cl_word = (int)(s.cull_geom.size() / 32);
-    for (const float4& g : s.clusters) s.cull_geom.push_back(finite4(g) && g.w >= 0.f ? g : make_float4(0.f, 0.f, 0.f, inf));
     pad32(); s.cull_leaf_word = (int)(s.cull_geom.size() / 32);
     for (size_t i = 0; i < s.leaf_geom.size(); ++i) {
         const float4 g = s.leaf_geom[i]; const int4 m = s.leaf_meta[i];
@@ -264,6 +275,8 @@ void build_host_arrays(const rt_scene_desc& d, rt_scene& s) {
         s.cull_geom.push_back(plain ? make_float4(g.x, g.y, g.z, std::fabs(g.w)) : make_float4(0.f, 0.f, 0.f, inf));
     }
     pad32(); s.cull_words = (int)(s.cull_geom.size() / 32);
+    s.cull_plane_bits.assign((size_t)std::max(s.cull_words, 1), 0u);
+    for (size_t i : planes) s.cull_plane_bits[i >> 5] |= 1u << (i & 31);
 }
 
 }  // namespace
@@ -340,7 +353,7 @@ int rt_scene_upload(const rt_scene_desc* d, rt_scene** out) {
         (rc = upload(s->lights, &s->d_lights)) || (rc = upload(s->fallbacks, &s->d_fallbacks)) ||
         (rc = upload(s->runs, &s->d_runs)) || (rc = upload(s->clusters, &s->d_clusters)) ||
         (rc = upload(s->obj_orig, &s->d_obj_orig)) || (rc = upload(s->masks, &s->d_masks)) ||
-        (rc = upload(s->cull_geom, &s->d_cull_geom))) { free_scene_locked(s); return rc; }
+        (rc = upload(s->cull_geom, &s->d_cull_geom)) || (rc = upload(s->cull_plane_bits, &s->d_cull_plane_bits))) { free_scene_locked(s); return rc; }
     rtd::SceneHeader& h = s->hdr;
     for (int k = 0; k < 3; ++k) { h.eye[k] = d->eye[k]; h.P[k] = d->screen_p[k]; h.bg[k] = d->background[k]; }
     h.lx = d->lx; h.ly = d->ly; h.nx = d->width; h.ny = d->height;
@@ -374,7 +387,7 @@ int rt_scene_upload(const rt_scene_desc* d, rt_scene** out) {
     // Scenes whose table is too long for a CTA to cull per round (> kMaxCullWords x 32 entries) scan without masks.
     constexpr int kMaxCullWords = 96;
     const bool cull = s->cull_words > 0 && s->cull_words <= kMaxCullWords && g_opts.cull != 0;
-    h.cull_geom = s->d_cull_geom; h.cull_words = cull ? s->cull_words : 0; h.cull_cl_word = s->cull_cl_word; h.cull_leaf_word = s->cull_leaf_word;
+    h.cull_geom = s->d_cull_geom; h.cull_words = cull ? s->cull_words : 0; h.cull_plane_bits = s->d_cull_plane_bits; h.cull_leaf_word = s->cull_leaf_word;
     h.off_cand_bytes = s->fits_const ? ((h.smem_bytes + 15) & ~15) : 0;
     s->smem_bytes = (size_t)h.off_cand_bytes + (cull ? sizeof(rtd::CandShared) + (size_t)(1 + rtd::kMaxListLights) * s->cull_words * 4 : 0);    *out = s;
     return RT_OK;
@@ -404,7 +417,7 @@ void free_scene_locked(rt_scene* s) {
     if (g_ctx.const_owner == s) g_ctx.const_owner = nullptr;
     cudaFree(s->d_obj_geom); cudaFree(s->d_obj_meta); cudaFree(s->d_leaf_geom); cudaFree(s->d_leaf_meta);
     cudaFree(s->d_pokeballs); cudaFree(s->d_affines); cudaFree(s->d_ops); cudaFree(s->d_materials);
-    cudaFree(s->d_lights); cudaFree(s->d_fallbacks); cudaFree(s->d_runs); cudaFree(s->d_clusters); cudaFree(s->d_obj_orig); cudaFree(s->d_masks); cudaFree(s->d_cull_geom);
+    cudaFree(s->d_lights); cudaFree(s->d_fallbacks); cudaFree(s->d_runs); cudaFree(s->d_clusters); cudaFree(s->d_obj_orig); cudaFree(s->d_masks); cudaFree(s->d_cull_geom); cudaFree(s->d_cull_plane_bits);
     delete s;
 }
 }  // namespace

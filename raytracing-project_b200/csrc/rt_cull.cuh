@@ -105,4 +105,18 @@ RT_CULL_FN bool bundle_rejects(const Bundle& b, Sphere4 g, float t_hi, bool segm
     return rej;
 }
 
+// Half-space surface (unit normal n, offset w = n.p0; HalfSpace::intersect, geometry.cpp:90-106): a ray hits it at
+// t = (w - n.o) / (n.d) > 0 only if it starts below the plane and runs upwards, or starts above and runs downwards.  Rejected
+// when every origin of the bundle is on one side and every direction leads away from the plane (or along it: |n.d| < 1e-12
+// is a miss as well).  The far end of the window is not used.
+RT_CULL_FN bool bundle_rejects_plane(const Bundle& b, Sphere4 g) {
+    const float no = fmaf(g.x, b.mx, fmaf(g.y, b.my, g.z * b.mz)) - g.w;          // signed distance of the central origin
+    const float nd = fmaf(g.x, b.cx, fmaf(g.y, b.cy, g.z * b.cz));
+    // b.kd = 1.002 delta + 1e-5 >= |n.(d_i - c)| + rounding;  b.h >= |o_i - m| incl. its own rounding margin
+    const float slack = b.h + 1e-5f * (fabsf(no) + fabsf(g.w)) + 1e-6f;
+    const bool above = no - slack > 0.f, below = no + slack < 0.f;
+    const bool up = nd - b.kd > 0.f, down = nd + b.kd < 0.f;
+    return (above && up) || (below && down);
+}
+
 }  // namespace rtd

@@ -39,10 +39,12 @@ struct SceneHeader {
     const float4* clusters;     // bounding sphere of every 16 consecutive primitives of a clustered run
     const int* obj_orig;        // JSON index of device object i (clustered runs are reordered spatially)
     const float4* masks;        // (c.xyz, |c|^2 - r^2 - 2^-16 (|c|^2 + r^2)) of every entry of obj_geom, leaf_geom, clusters (in that order)
-    // round-level culling (rt_cull.cuh): (centre, radius | inf) of objects | bounds | leaves, every section padded to a
-    // multiple of 32 with w < 0; candidate bit of object i: cull_obj_word*32 + i (= i), of bound i: cull_cl_word*32 + i, ...
+    // round-level culling (rt_cull.cuh): (centre, radius | inf) of objects | leaves — a generic object is represented by its
+    // world bound, a plain half-space by (n, n.p0) with its bit set in cull_plane_bits — both sections padded to a multiple of
+    // 32 with w < 0; candidate bit of object i: i, of leaf i: cull_leaf_word * 32 + i
     const float4* cull_geom;
-    int cull_words, cull_cl_word, cull_leaf_word;     // words per bundle (0: scene not culled), first word of the bound / leaf section
+    const uint32_t* cull_plane_bits;                  // one bit per entry: the entry is a half-space surface
+    int cull_words, cull_leaf_word;                   // words per bundle (0: scene not culled), first word of the leaf section
     int off_cand_bytes;                               // CandShared + masks in dynamic shared memory
 };
 
@@ -153,8 +155,9 @@ struct Counters { unsigned primary, shadow, secondary, tests; };
 
 // ---- candidate masks of one round (rt_cull.cuh) ---------------------------------------------------------
 // A CTA traces 256 samples = 32 neighbouring pixels per round.  Before the camera rays are traced, and again before their
-// shadow rays are, the CTA culls EVERY cullable entry of the scene — top-level objects, cluster / object bounds, CSG
-// leaves: the table c_hdr.cull_geom, (centre, radius) or radius = inf for entries that cannot be culled — against the
+// shadow rays are, the CTA culls EVERY cullable entry of the scene — top-level objects (CSG programs and wrapped primitives
+// by their world bound, half-spaces as planes) and CSG leaves: the table c_hdr.cull_geom, (centre, radius) or radius = inf
+// for entries that cannot be culled — against the
 // round's bundle, one entry per thread, and leaves one candidate bit per entry in shared memory: bundle 0 = the camera
 // rays, bundle 1 + l = the shadow rays towards light l (l < kMaxListLights).  The scans then take their candidates from
 // these words instead of testing every primitive per ray.  The boxes the bundles are built from are reduced with CREDUX
@@ -198,7 +201,14 @@ __device__ __forceinline__ void cand_box_add(bool use, V3 v, int* lo, int* hi, i
 // All threads of the CTA, after a barrier that follows the box reductions: bundles [b0, b0 + nb) x all entry words are
 // dealt to the warps; a warp builds the bundle it is working on (the same arithmetic in every lane), culls 32 entries and
 // lane 0 stores the ballot.  b = 0: camera rays; b >= 1: shadow rays towards light b - 1.  Ends with a barrier.
+#ifndef RT_CAND_NOINLINE
+#define RT_CAND_NOINLINE 0        // A/B: 1 = one out-of-line copy of cand_build (camera and shadow masks share it)
+#endif
+#if RT_CAND_NOINLINE
+__device__ __noinline__ void cand_build(int b0, int nb, unsigned& tests) {
+#else
 __device__ __forceinline__ void cand_build(int b0, int nb, unsigned& tests) {
+#endif
     CandShared* S = cand_shared();
     const int W = c_hdr.cull_words, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
     const bool nan = b0 == 0 ? (S->nan_flags & 1) : (S->nan_flags & 2);
@@ -223,9 +233,10 @@ __device__ __forceinline__ void cand_build(int b0, int nb, unsigned& tests) {
             if (w == 0 && lane == 0) S->wide[b] = B.wide;
             if (B.wide) continue;
             const float4 g = __ldg(c_hdr.cull_geom + 32 * w + lane);
+            const bool plane = (__ldg(c_hdr.cull_plane_bits + w) >> lane) & 1u;
             Sphere4 q; q.x = g.x; q.y = g.y; q.z = g.z; q.w = g.w;
             // padding entries have w < 0; CSG leaves (words from cull_leaf_word on) are culled on the whole line
-            const bool cand = g.w >= 0.f && !bundle_rejects(B, q, B.t_hi, w < c_hdr.cull_leaf_word);
+            const bool cand = plane ? !bundle_rejects_plane(B, q) : (g.w >= 0.f && !bundle_rejects(B, q, B.t_hi, w < c_hdr.cull_leaf_word));
             ++tests;
             const uint32_t bits = __ballot_sync(kFullWarp, cand);
             if (lane == 0) cand_words(b)[w] = bits;

@@ -65,46 +65,77 @@ __device__ __forceinline__ bool generic_hit(int i, V3 o, V3 d, float tmin, float
     return true;
 }
 
-// ---- Scene::intersect (scene.cpp:10-24) and Scene::occluded (scene.cpp:33-42): ONE scan -------------------------------
+// ---- Scene::intersect (scene.cpp:10-24) and Scene::occluded (scene.cpp:33-42): ONE scan per kind of ray -----------------
 // Both queries walk the object list in JSON order; `any` (Scene::occluded) stops at the first accepted hit, otherwise the
 // window's far end shrinks to the best hit so far (tmax == best_t until the first hit, so the two are the same loop).
-// Per run the candidates come from the round's mask `cand` (bits of objects | bounds | leaves, see rt_device.cuh) or,
-// without one, from the per-lane conservative mask (sphere_mask); every candidate is finished in JSON order with exactly
-// the reference's root selection and window test, so the result equals a one-by-one scan.  Any-hit walks the runs
-// backwards (the order cannot be observed, scene.cpp:33-42 returns a bool, and later objects are usually the foreground
-// detail that casts the shadows).
+// Every candidate is finished in JSON order with exactly the reference's root selection and window test, so the result
+// equals a one-by-one scan.
 struct ScanResult { int best; float t; uint32_t code; float tent; };
 
+// (1) A ray of a round's bundle (camera rays, their shadow rays): the candidates are the set bits of the round's mask
+// `cand` (rt_device.cuh cand_build) — objects in device order, then the CSG leaves.  A handful of bits per query.
 template <bool C, bool K>
-__device__ __forceinline__ void scan_body(V3 o, V3 d, float tmin, float tmax, const bool any, const uint32_t* cand, ScanResult& res, unsigned& tests) {
+__device__ __forceinline__ void scan_masked(V3 o, V3 d, float tmin, float tmax, const bool any, const uint32_t* cand, ScanResult& res, unsigned& tests) {
     int best = -1; float best_t = tmax; uint32_t best_code = 0; float best_tent = 0.f;
-    const uint32_t* boundw = cand ? cand + c_hdr.cull_cl_word : nullptr;       // section of the cluster / object bounds
-    const uint32_t* leafw = cand ? cand + c_hdr.cull_leaf_word : nullptr;      // section of the CSG leaves
+    const int W = c_hdr.cull_leaf_word;
+    const uint32_t* leafw = cand + W;
+    for (int w = 0; w < W; ++w) {
+        uint32_t bits = cand[w];
+        while (bits) {
+            const int i = (w << 5) + __ffs(bits) - 1; bits &= bits - 1;
+            const int4 m = SV<C>::obj_meta(i);
+            const int kind = m.x & 0xff;
+            float t;
+            if ((m.x >> 8) == 0 && kind != RT_PRIM_PROGRAM) {
+                ++tests;
+                const float4 g = SV<C>::template obj_geom_k<K>(i);
+                if (!(kind == RT_PRIM_HALFSPACE ? plane_t(g, o, d, tmin, best_t, t) : sphere_t(g, o, d, tmin, best_t, t))) continue;
+                // clustered runs are reordered spatially: exact ties go to the later JSON index as in scene.cpp:15-21
+                if (K && t == best_t && best >= 0 && SV<C>::obj_orig(i) < SV<C>::obj_orig(best)) continue;
+                best = i; best_t = t;
+            } else {
+                float tent; uint32_t code;
+                if (!generic_hit<C, K>(i, o, d, tmin, best_t, leafw, t, code, tent, tests)) continue;
+                best = i; best_t = t; best_code = code; best_tent = tent;
+            }
+            if (any) goto done;
+        }
+    }
+done:
+    res.best = best; res.t = best_t; res.code = best_code; res.tent = best_tent;
+}
+
+// (2) A ray that belongs to no bundle (secondary rays, known-answer rays, rounds whose bundle is too wide): run by run,
+// the candidates of a run from the per-lane conservative mask (sphere_mask).  Scenes of a few dozen primitives walk the
+// runs backwards for any-hit (the order cannot be observed, scene.cpp:33-42 returns a bool, and later objects are usually
+// the foreground detail that casts the shadows).
+template <bool C, bool K>
+__device__ __forceinline__ void scan_body(V3 o, V3 d, float tmin, float tmax, const bool any, ScanResult& res, unsigned& tests) {
+    int best = -1; float best_t = tmax; uint32_t best_code = 0; float best_tent = 0.f;
     const int n_runs = c_hdr.n_runs;
     for (int rr = 0; rr < n_runs; ++rr) {
-        const int4 run = SV<C>::run(any ? n_runs - 1 - rr : rr);
+        const int4 run = SV<C>::run((any && !K) ? n_runs - 1 - rr : rr);
         const int first = run.y, end = run.y + run.z;
         if (K && (run.x == RUN_SPHERE || run.x == RUN_POKEBALL) && run.w > 0) {
-            // Clustered run (spatially reordered, 16 primitives per cluster): the clusters whose bound is a candidate, then
-            // their members.  A sphere's candidate root does not depend on the order of the scan; exact ties go to the later
-            // JSON index as in scene.cpp:15-21.
+            // Clustered run (spatially reordered, 16 primitives per cluster): candidate mask over the cluster bounds, then
+            // over the members of the clusters whose bound overlaps the window.  A sphere's candidate root does not depend on
+            // the order of the scan; exact ties go to the later JSON index as in scene.cpp:15-21.
             const int ctab = run.w - 1, ncl = (run.z + 15) >> 4;
+            tests += ncl;
             for (int cb = 0; cb < ncl; cb += 32) {
-                const int ncb = min(32, ncl - cb);
-                uint32_t bits = candidates<C>(boundw, ctab + cb, SV<C>::cluster_ptr(ctab + cb), ncb, o, d, tests);
-                while (bits) {
-                    const int c = cb + __ffs(bits) - 1; bits &= bits - 1;
-                    if (!cand) {                                      // the round's mask already knows the window
-                        float hb;
-                        const float disc = sphere_disc(SV<C>::cluster(ctab + c), o, d, hb);
-                        const float sq = sqrtf(disc);
-                        if (-hb + sq < 0.f || -hb - sq > best_t) continue;
-                    }
+                uint32_t cmask = sphere_mask<C>(SV<C>::cluster_ptr(ctab + cb), min(32, ncl - cb), o, d);
+                while (cmask) {
+                    const int c = cb + __ffs(cmask) - 1; cmask &= cmask - 1;
+                    float hb;
+                    const float disc = sphere_disc(SV<C>::cluster(ctab + c), o, d, hb);
+                    const float sq = sqrtf(disc);
+                    if (-hb + sq < 0.f || -hb - sq > best_t) continue;
                     const int m0 = first + 16 * c, n = min(16, end - m0);
-                    uint32_t mask = candidates<C>(cand, m0, SV<C>::obj_ptr(m0), n, o, d, tests);
+                    tests += n;
+                    uint32_t mask = sphere_mask<C>(SV<C>::obj_ptr(m0), n, o, d);
                     while (mask) {
                         const int i = m0 + __ffs(mask) - 1; mask &= mask - 1;
-                        float t; ++tests;
+                        float t;
                         if (!sphere_t(SV<C>::template obj_geom_k<K>(i), o, d, tmin, best_t, t)) continue;
                         if (t == best_t && best >= 0 && SV<C>::obj_orig(i) < SV<C>::obj_orig(best)) continue;
                         best = i; best_t = t;
@@ -115,10 +146,11 @@ __device__ __forceinline__ void scan_body(V3 o, V3 d, float tmin, float tmax, co
         } else if (run.x == RUN_SPHERE || run.x == RUN_POKEBALL) {
             for (int c0 = first; c0 < end; c0 += 32) {                       // candidates first, finished in JSON order
                 const int n = min(32, end - c0);
-                uint32_t mask = candidates<C>(cand, c0, SV<C>::obj_ptr(c0), n, o, d, tests);
+                tests += n;
+                uint32_t mask = sphere_mask<C>(SV<C>::obj_ptr(c0), n, o, d);
                 while (mask) {
                     const int i = c0 + __ffs(mask) - 1; mask &= mask - 1;
-                    float t; ++tests;
+                    float t;
                     if (sphere_t(SV<C>::template obj_geom_k<K>(i), o, d, tmin, best_t, t)) { best = i; best_t = t; if (any) goto done; }
                 }
             }
@@ -128,15 +160,17 @@ __device__ __forceinline__ void scan_body(V3 o, V3 d, float tmin, float tmax, co
                 if (plane_t(SV<C>::template obj_geom_k<K>(i), o, d, tmin, best_t, t)) { best = i; best_t = t; if (any) goto done; }
             }
         } else {
-            // generic objects (CSG programs, wrapped / affine primitives): one world bound per object (R = inf: unknown)
+            // generic objects (CSG programs, wrapped / affine primitives): one world bound per object (R = inf: unknown),
+            // scanned with the candidate mask before the object itself is looked at
             const int ctab = run.w - 1;
+            tests += run.z;
             for (int c0 = first; c0 < end; c0 += 32) {
                 const int n = min(32, end - c0);
-                uint32_t bits = candidates<C>(boundw, ctab + c0 - first, SV<C>::cluster_ptr(ctab + c0 - first), n, o, d, tests);
-                while (bits) {
-                    const int i = c0 + __ffs(bits) - 1; bits &= bits - 1;
+                uint32_t mask = sphere_mask<C>(SV<C>::cluster_ptr(ctab + c0 - first), n, o, d);
+                while (mask) {
+                    const int i = c0 + __ffs(mask) - 1; mask &= mask - 1;
                     float t, tent; uint32_t code;
-                    if (generic_hit<C, K>(i, o, d, tmin, best_t, leafw, t, code, tent, tests)) {
+                    if (generic_hit<C, K>(i, o, d, tmin, best_t, nullptr, t, code, tent, tests)) {
                         best = i; best_t = t; best_code = code; best_tent = tent;
                         if (any) goto done;
                     }
@@ -148,22 +182,26 @@ done:
     res.best = best; res.t = best_t; res.code = best_code; res.tent = best_tent;
 }
 
-// Scenes with clustered runs (K: ~10^3 primitives) keep ONE out-of-line copy of the scan for both queries: all warps of an
+// Scenes with clustered runs (K: ~10^3 primitives) keep ONE out-of-line copy of scan (2) for both queries: all warps of an
 // SM spend most of their time in this one function, so its code stays resident in the instruction cache (synthetic-A 2K
 // 29.0 -> 23.7 ms when this was introduced).  Scenes of a few dozen primitives inline the two specialisations (the call
 // cost them more than it saved).  The test count is returned by value (a reference would pin the caller's counter to
 // local memory).
 struct ScanOut { ScanResult r; unsigned tests; };
 template <bool C, bool K>
-__device__ __noinline__ ScanOut scan_shared(V3 o, V3 d, float tmin, float tmax, bool any, const uint32_t* cand) {
+__device__ __noinline__ ScanOut scan_shared(V3 o, V3 d, float tmin, float tmax, bool any) {
     ScanOut out; out.tests = 0;
-    scan_body<C, K>(o, d, tmin, tmax, any, cand, out.r, out.tests);
+    scan_body<C, K>(o, d, tmin, tmax, any, out.r, out.tests);
     return out;
 }
+#ifndef RT_SCAN_SHARED
+#define RT_SCAN_SHARED 0          // A/B: 1 = the out-of-line scan for every scene
+#endif
 template <bool C, bool K, bool ANY>
 __device__ __forceinline__ void scan(V3 o, V3 d, float tmin, float tmax, const uint32_t* cand, ScanResult& res, Counters& cnt) {
-    if (K) { const ScanOut so = scan_shared<C, K>(o, d, tmin, tmax, ANY, cand); res = so.r; cnt.tests += so.tests; }
-    else scan_body<C, K>(o, d, tmin, tmax, ANY, cand, res, cnt.tests);
+    if (cand) scan_masked<C, K>(o, d, tmin, tmax, ANY, cand, res, cnt.tests);
+    else if (K || RT_SCAN_SHARED) { const ScanOut so = scan_shared<C, K>(o, d, tmin, tmax, ANY); res = so.r; cnt.tests += so.tests; }
+    else scan_body<C, K>(o, d, tmin, tmax, ANY, res, cnt.tests);
 }
 
 template <bool C, bool K>

@@ -134,6 +134,55 @@ int main(int argc, char** argv) {
             }
         }
     }
+    // ---- half-spaces: plane_t (rt_device.cuh) restated; planes through / near the bundle's origins, normals near-orthogonal to the rays
+    long long pcases = 0, prej = 0;
+    for (long long tr = 0; tr < trials / 4; ++tr) {
+        const double S = scales[tr % 4], hh = hs[(tr / 4) % 5] * (S > 100 ? 10 : 1), dl = deltas[(tr / 20) % 6];
+        V o[32], d[32]; float tmax[32];
+        auto c0 = unit();
+        const double m0[3] = {(2 * U(rng) - 1) * S, (2 * U(rng) - 1) * S, (2 * U(rng) - 1) * S};
+        for (int i = 0; i < 32; ++i) {
+            auto u = unit(); const double ro = (i == 16 ? 0.0 : hh * std::cbrt(U(rng)));
+            o[i] = {(float)(m0[0] + ro * u[0]), (float)(m0[1] + ro * u[1]), (float)(m0[2] + ro * u[2])};
+            auto w = unit(); const double rd = (i == 16 ? 0.0 : dl * U(rng));
+            double x = c0[0] + rd * w[0], y = c0[1] + rd * w[1], z = c0[2] + rd * w[2], L = std::sqrt(x * x + y * y + z * z);
+            d[i] = {(float)(x / L), (float)(y / L), (float)(z / L)};
+            tmax[i] = INFINITY;
+        }
+        rtd::Bundle B{};
+        B.mx = o[16].x; B.my = o[16].y; B.mz = o[16].z; B.cx = d[16].x; B.cy = d[16].y; B.cz = d[16].z;
+        float h2 = 0.f, d2 = 0.f;
+        for (int i = 0; i < 32; ++i) {
+            const float ax = o[i].x - B.mx, ay = o[i].y - B.my, az = o[i].z - B.mz, bx = d[i].x - B.cx, by = d[i].y - B.cy, bz = d[i].z - B.cz;
+            h2 = fmaxf(h2, fmaf(ax, ax, fmaf(ay, ay, az * az))); d2 = fmaxf(d2, fmaf(bx, bx, fmaf(by, by, bz * bz)));
+        }
+        rtd::bundle_finish(B, h2, d2, INFINITY);
+        if (B.wide) continue;
+        for (int k = 0; k < 16; ++k) {
+            auto n = unit();
+            if (k % 2) {                                             // nearly orthogonal to the central direction
+                const double nc = n[0] * c0[0] + n[1] * c0[1] + n[2] * c0[2], a = (k % 4 == 1 ? 1.0 : 1e-3) * (2 * U(rng) - 1) * (dl + 1e-6) * 2;
+                double x = n[0] - (nc - a) * c0[0], y = n[1] - (nc - a) * c0[1], z = n[2] - (nc - a) * c0[2], L = std::sqrt(x * x + y * y + z * z);
+                n = {x / L, y / L, z / L};
+            }
+            const int i = (int)(U(rng) * 32) & 31;
+            const double off = (k % 3 == 0 ? (2 * U(rng) - 1) * (hh + 1e-4) * 2 : (2 * U(rng) - 1) * S);    // plane near an origin, or anywhere
+            rtd::Sphere4 g{(float)n[0], (float)n[1], (float)n[2], 0.f};
+            g.w = (float)(g.x * (double)o[i].x + g.y * (double)o[i].y + g.z * (double)o[i].z + off);
+            ++pcases;
+            if (!rtd::bundle_rejects_plane(B, g)) continue;
+            ++prej;
+            for (int j = 0; j < 32; ++j) {                            // plane_t with tmin = 1e-4, tmax = inf
+                const float nd = fmaf(g.x, d[j].x, fmaf(g.y, d[j].y, g.z * d[j].z));
+                if (fabsf(nd) < 1e-12f) continue;
+                const float no = fmaf(g.x, o[j].x, fmaf(g.y, o[j].y, g.z * o[j].z));
+                const float tt = (g.w - no) / nd;
+                if (!(tt < 1e-4f || tt > tmax[j]) && ++bad <= 10) std::printf("# plane violation: scale %g h %g delta %g lane %d t %g\n", S, hh, dl, j, (double)tt);
+            }
+        }
+    }
+    cases += pcases; rejected += prej;
+    std::printf("# planes: %lld cases, %lld rejected\n", pcases, prej);
     std::printf("%lld %lld %lld\n", cases, rejected, bad);
     return bad ? 1 : 0;
 }
