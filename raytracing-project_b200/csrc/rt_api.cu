@@ -307,15 +307,20 @@ int rt_init(int device) {
     CU(cudaMemcpy(g_ctx.mt_resume, seed, sizeof(seed), cudaMemcpyHostToDevice));
     g_ctx.mt_tiles = 0; g_ctx.mt_capacity = 0; g_ctx.mt_table = nullptr; g_ctx.const_owner = nullptr;
     g_ctx.mt_resume_tiles = 0; g_ctx.d_jump_poly = nullptr;
-    CU(cudaFuncSetAttribute(rtd::render_standard_kernel<true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget + 4096));
-    CU(cudaFuncSetAttribute(rtd::render_standard_kernel<true, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget + 4096));
-    CU(cudaFuncSetAttribute(rtd::render_standard_kernel<true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget + 4096));
-    CU(cudaFuncSetAttribute(rtd::render_standard_kernel<true, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget + 4096));
-    CU(cudaFuncSetAttribute(rtd::render_wavefront_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget + 4096));
-    CU(cudaFuncSetAttribute(rtd::render_wavefront_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget + 4096));
-    CU(cudaFuncSetAttribute(rtd::paper_gbuffer_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget + 4096));
-    CU(cudaFuncSetAttribute(rtd::paper_gbuffer_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget + 4096));
-    CU(cudaFuncSetAttribute(rtd::trace_rays_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSceneSmemBudget + 4096));
+    const int dyn_smem = (int)kSceneSmemBudget + 4096;
+    CU(cudaFuncSetAttribute(rtd::render_standard_kernel<true, false, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_smem));
+    CU(cudaFuncSetAttribute(rtd::render_standard_kernel<true, false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_smem));
+    CU(cudaFuncSetAttribute(rtd::render_standard_kernel<true, false, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_smem));
+    CU(cudaFuncSetAttribute(rtd::render_standard_kernel<true, false, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_smem));
+    CU(cudaFuncSetAttribute(rtd::render_standard_kernel<true, true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_smem));
+    CU(cudaFuncSetAttribute(rtd::render_standard_kernel<true, true, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_smem));
+    CU(cudaFuncSetAttribute(rtd::render_wavefront_kernel<true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_smem));
+    CU(cudaFuncSetAttribute(rtd::render_wavefront_kernel<true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_smem));
+    CU(cudaFuncSetAttribute(rtd::render_wavefront_kernel<true, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_smem));
+    CU(cudaFuncSetAttribute(rtd::paper_gbuffer_kernel<true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_smem));
+    CU(cudaFuncSetAttribute(rtd::paper_gbuffer_kernel<true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_smem));
+    CU(cudaFuncSetAttribute(rtd::paper_gbuffer_kernel<true, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_smem));
+    CU(cudaFuncSetAttribute(rtd::trace_rays_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_smem));
     g_ctx.ready = true;
     return RT_OK;
 }
@@ -385,8 +390,13 @@ int rt_scene_upload(const rt_scene_desc* d, rt_scene** out) {
     if (g_opts.global_scene == 1) s->fits_const = false;                    // test hook: the global-memory path on any scene
     // Round-level culling: masks of (1 + kMaxListLights) bundles behind the staged scene (or alone, on the global path).
     // Scenes whose table is too long for a CTA to cull per round (> kMaxCullWords x 32 entries) scan without masks.
-    constexpr int kMaxCullWords = 96;
-    const bool cull = s->cull_words > 0 && s->cull_words <= kMaxCullWords && g_opts.cull != 0;
+    // Round-level masks pay when a scan is more than a handful of tests and the table is short enough for a CTA to cull per
+    // round: not for scenes of a few primitives (pokeballs: 4 objects), not for clustered scenes (their scans already walk a
+    // spatial structure; culling 1 300 entries per bundle and round cost more than it saved: synthetic-A 2K 23.8 -> 41 ms).
+    constexpr int kMaxCullWords = 8, kMinCullEntries = 10;
+    bool cull = s->cull_words > 0 && s->cull_words <= kMaxCullWords && !s->clustered && d->n_objects + d->n_leaves >= kMinCullEntries;
+    if (g_opts.cull == 0) cull = false;
+    if (g_opts.cull == 1) cull = s->cull_words > 0 && s->cull_words <= 96 && !s->clustered;        // test hook: masks wherever they can be built
     h.cull_geom = s->d_cull_geom; h.cull_words = cull ? s->cull_words : 0; h.cull_plane_bits = s->d_cull_plane_bits; h.cull_leaf_word = s->cull_leaf_word;
     h.off_cand_bytes = s->fits_const ? ((h.smem_bytes + 15) & ~15) : 0;
     s->smem_bytes = (size_t)h.off_cand_bytes + (cull ? sizeof(rtd::CandShared) + (size_t)(1 + rtd::kMaxListLights) * s->cull_words * 4 : 0);    *out = s;
@@ -551,8 +561,11 @@ int launch_frame(rt_scene* s, int mode, int rank, int world, uchar4* rgba8, floa
         { int rc2 = grow(&g_ctx.d_gbuf, &g_ctx.gbuf_cap, (size_t)npx * sizeof(rtd::GBuf)); if (rc2) return rc2; }
         const unsigned blocks = (unsigned)((npx + 255) / 256);
         // kernel variant: <scene staged in shared memory, scene has clustered runs>
-        auto paper = s->fits_const ? (!s->clustered ? rtd::paper_gbuffer_kernel<true, false> : rtd::paper_gbuffer_kernel<true, true>)
-                                   : (!s->clustered ? rtd::paper_gbuffer_kernel<false, false> : rtd::paper_gbuffer_kernel<false, true>);
+        // kernel variant: <scene staged in shared memory, clustered runs, round-level masks>
+        const bool mm = s->hdr.cull_words != 0;
+        auto paper = s->clustered ? (s->fits_const ? rtd::paper_gbuffer_kernel<true, true, false> : rtd::paper_gbuffer_kernel<false, true, false>)
+                   : s->fits_const ? (mm ? rtd::paper_gbuffer_kernel<true, false, true> : rtd::paper_gbuffer_kernel<true, false, false>)
+                                   : (mm ? rtd::paper_gbuffer_kernel<false, false, true> : rtd::paper_gbuffer_kernel<false, false, false>);
         paper<<<blocks, 256, s->smem_bytes, st>>>(g_ctx.d_gbuf, ids, g_ctx.counters, rank, world);
         rtd::paper_post_kernel<<<blocks, 256, 0, st>>>(g_ctx.d_gbuf, rgba8, rgbf, s->width, s->height, rank, world);
         CU(cudaGetLastError());
@@ -567,15 +580,22 @@ int launch_frame(rt_scene* s, int mode, int rank, int world, uchar4* rgba8, floa
     prm.counters = g_ctx.counters; prm.tile_counter = g_ctx.tile_counter;
     prm.n_local_tiles = (int)local; prm.rank = rank; prm.world = world; prm.n_pixels = npx;
     CU(cudaMemsetAsync(g_ctx.tile_counter, 0, sizeof(unsigned), st));
-    // kernel variant: <scene staged in shared memory, scene has bounds>; ray trees deeper than 1 -> wavefront kernel
-    const bool kk = s->clustered;
-    auto kernel = s->bounces
-        ? (s->fits_const ? (kk ? rtd::render_wavefront_kernel<true, true> : rtd::render_wavefront_kernel<true, false>)
-                         : (kk ? rtd::render_wavefront_kernel<false, true> : rtd::render_wavefront_kernel<false, false>))
-        : s->flat ? (s->fits_const ? (kk ? rtd::render_standard_kernel<true, true, true> : rtd::render_standard_kernel<true, false, true>)
-                                   : (kk ? rtd::render_standard_kernel<false, true, true> : rtd::render_standard_kernel<false, false, true>))
-                  : (s->fits_const ? (kk ? rtd::render_standard_kernel<true, true, false> : rtd::render_standard_kernel<true, false, false>)
-                                   : (kk ? rtd::render_standard_kernel<false, true, false> : rtd::render_standard_kernel<false, false, false>));
+    // kernel variant: <scene staged in shared memory, clustered runs, [flat], round-level masks>; deep ray trees -> wavefront kernel
+    const bool kk = s->clustered, cc = s->fits_const, mm = s->hdr.cull_words != 0;      // (clustered scenes never have masks)
+    void (*kernel)(rtd::RenderParams) = nullptr;
+    if (s->bounces) {
+        kernel = kk ? (cc ? rtd::render_wavefront_kernel<true, true, false> : rtd::render_wavefront_kernel<false, true, false>)
+               : cc ? (mm ? rtd::render_wavefront_kernel<true, false, true> : rtd::render_wavefront_kernel<true, false, false>)
+                    : (mm ? rtd::render_wavefront_kernel<false, false, true> : rtd::render_wavefront_kernel<false, false, false>);
+    } else if (s->flat) {
+        kernel = kk ? (cc ? rtd::render_standard_kernel<true, true, true, false> : rtd::render_standard_kernel<false, true, true, false>)
+               : cc ? (mm ? rtd::render_standard_kernel<true, false, true, true> : rtd::render_standard_kernel<true, false, true, false>)
+                    : (mm ? rtd::render_standard_kernel<false, false, true, true> : rtd::render_standard_kernel<false, false, true, false>);
+    } else {
+        kernel = kk ? (cc ? rtd::render_standard_kernel<true, true, false, false> : rtd::render_standard_kernel<false, true, false, false>)
+               : cc ? (mm ? rtd::render_standard_kernel<true, false, false, true> : rtd::render_standard_kernel<true, false, false, false>)
+                    : (mm ? rtd::render_standard_kernel<false, false, false, true> : rtd::render_standard_kernel<false, false, false, false>);
+    }
     const size_t smem = s->smem_bytes;
     int per_sm = 0;
     const int threads = rtd::kRenderThreads;

@@ -167,8 +167,7 @@ struct CandShared {
     int dir_lo[3], dir_hi[3];              // camera rays: box of the directions
     int org_lo[3], org_hi[3];              // shadow rays: box of the origins
     int eps_max, nan_flags;                // largest shadow epsilon; bit 0 / 1: a NaN in the first / second box
-    int wide[1 + kMaxListLights];          // bundle b culls nothing (or was not built): scan without a mask
-    int pad[3];
+    int pad[2];
     // followed by (1 + kMaxListLights) * c_hdr.cull_words mask words
 };
 __device__ __forceinline__ CandShared* cand_shared() { return reinterpret_cast<CandShared*>(s_scene + c_hdr.off_cand_bytes); }
@@ -185,7 +184,6 @@ __device__ __forceinline__ void cand_init() {
     CandShared* S = cand_shared();
     if (threadIdx.x < 3) { S->dir_lo[threadIdx.x] = kOrdPosInf; S->dir_hi[threadIdx.x] = kOrdNegInf; S->org_lo[threadIdx.x] = kOrdPosInf; S->org_hi[threadIdx.x] = kOrdNegInf; }
     if (threadIdx.x == 3) { S->eps_max = 0; S->nan_flags = 0; }
-    if (threadIdx.x < 1 + kMaxListLights) S->wide[threadIdx.x] = 1;
     __syncthreads();
 }
 // One warp: add the vectors v of its lanes with `use` to a box (lo, hi in shared memory).
@@ -202,7 +200,7 @@ __device__ __forceinline__ void cand_box_add(bool use, V3 v, int* lo, int* hi, i
 // dealt to the warps; a warp builds the bundle it is working on (the same arithmetic in every lane), culls 32 entries and
 // lane 0 stores the ballot.  b = 0: camera rays; b >= 1: shadow rays towards light b - 1.  Ends with a barrier.
 #ifndef RT_CAND_NOINLINE
-#define RT_CAND_NOINLINE 0        // A/B: 1 = one out-of-line copy of cand_build (camera and shadow masks share it)
+#define RT_CAND_NOINLINE 1        // one out-of-line copy of cand_build: camera and shadow masks share it (snorlax 4K 11.87 -> 11.35 ms)
 #endif
 #if RT_CAND_NOINLINE
 __device__ __noinline__ void cand_build(int b0, int nb, unsigned& tests) {
@@ -217,9 +215,9 @@ __device__ __forceinline__ void cand_build(int b0, int nb, unsigned& tests) {
     for (int k = 0; k < 3; ++k) { lo[k] = ord2f(b0 == 0 ? S->dir_lo[k] : S->org_lo[k]); hi[k] = ord2f(b0 == 0 ? S->dir_hi[k] : S->org_hi[k]); }
     const bool empty = !(lo[0] <= hi[0]);                         // no ray contributed: nothing will be asked
     const float eps_max = __int_as_float(S->eps_max);
-    int cur = -1; Bundle B; B.wide = 1; B.t_hi = 0.f;
+    int cur = -1; Bundle B; B.wide = 1; B.t_hi = 0.f; B.h = 0.f; B.kd = 0.f; B.inv1md = 1.f; B.mx = B.my = B.mz = 0.f; B.cx = B.cy = B.cz = 0.f;
     if (!empty && !nan) {
-        for (int k = threadIdx.x >> 5; k < nb * W; k += nwarps) {
+        for (int k = threadIdx.x >> 5; k < nb * W; k += nwarps) {   // (empty and no NaN: no ray will ask)
             const int bb = k / W, w = k - bb * W, b = b0 + bb;
             if (bb != cur) {
                 cur = bb;
@@ -230,24 +228,27 @@ __device__ __forceinline__ void cand_build(int b0, int nb, unsigned& tests) {
                     bundle_from_box_light(B, lo, hi, eps_max, L, lp.w != 0.f);
                 }
             }
-            if (w == 0 && lane == 0) S->wide[b] = B.wide;
-            if (B.wide) continue;
             const float4 g = __ldg(c_hdr.cull_geom + 32 * w + lane);
             const bool plane = (__ldg(c_hdr.cull_plane_bits + w) >> lane) & 1u;
             Sphere4 q; q.x = g.x; q.y = g.y; q.z = g.z; q.w = g.w;
             // padding entries have w < 0; CSG leaves (words from cull_leaf_word on) are culled on the whole line
-            const bool cand = plane ? !bundle_rejects_plane(B, q) : (g.w >= 0.f && !bundle_rejects(B, q, B.t_hi, w < c_hdr.cull_leaf_word));
+            // (a bundle too wide to cull — a round across a silhouette, a light inside the box — keeps every entry)
+            const bool cand = B.wide ? !(g.w < 0.f) : plane ? !bundle_rejects_plane(B, q) : (g.w >= 0.f && !bundle_rejects(B, q, B.t_hi, w < c_hdr.cull_leaf_word));
             ++tests;
             const uint32_t bits = __ballot_sync(kFullWarp, cand);
             if (lane == 0) cand_words(b)[w] = bits;
         }
-    } else if (threadIdx.x < nb) S->wide[b0 + threadIdx.x] = 1;
+    } else if (nan) {                                             // a NaN among the rays: keep every entry
+        for (int k = threadIdx.x >> 5; k < nb * W; k += nwarps) {
+            const int bb = k / W, w = k - bb * W;
+            const uint32_t bits = __ballot_sync(kFullWarp, !(__ldg(c_hdr.cull_geom + 32 * w + lane).w < 0.f));
+            if (lane == 0) cand_words(b0 + bb)[w] = bits;
+        }
+    }
     __syncthreads();
 }
-// Candidate words of bundle b for the scans, or nullptr when the bundle culls nothing.
-__device__ __forceinline__ const uint32_t* cand_of(int b) {
-    return (c_hdr.cull_words && b <= kMaxListLights && !cand_shared()->wide[b]) ? cand_words(b) : nullptr;
-}
+// Candidate words of bundle b for the scans (nullptr: light beyond kMaxListLights, scanned without a mask).
+__device__ __forceinline__ const uint32_t* cand_of(int b) { return b <= kMaxListLights ? cand_words(b) : nullptr; }
 // Candidate bits of entries [first, first + n), n <= 32, of a word array (nullptr: all of them).
 __device__ __forceinline__ uint32_t cand_bits(const uint32_t* words, int first, int n) {
     const uint32_t all = n >= 32 ? 0xffffffffu : ((1u << n) - 1u);

@@ -149,8 +149,9 @@ __device__ __forceinline__ const uint32_t* camera_mask(bool active, V3 d, Counte
 #endif
 constexpr int kRenderThreads = 256;
 
-// F ("flat"): no ray of the scene can spawn a child, see ray_step.
-template <bool C, bool K, bool F>
+// F ("flat"): no ray of the scene can spawn a child, see ray_step.  M: round-level masks (rt_device.cuh cand_*): the tile
+// is walked in CTA-wide rounds with barriers; kernels without M contain none of that code.
+template <bool C, bool K, bool F, bool M>
 __global__ void __launch_bounds__(kRenderThreads, RT_MIN_BLOCKS) render_standard_kernel(RenderParams prm) {
     // raw generator words: [0, kN) the tile's checkpoint, then the 8 blocks it yields (tempered on use)
     __shared__ __align__(16) uint32_t raw[mt::kN + mt::kOutputsPerTile];
@@ -161,7 +162,7 @@ __global__ void __launch_bounds__(kRenderThreads, RT_MIN_BLOCKS) render_standard
     const int nx = c_hdr.nx, ny = c_hdr.ny;
     Counters cnt = {0, 0, 0, 0};
     stage_scene<C>();
-    cand_init();
+    if (M) cand_init();
     for (;;) {
         if (tid == 0) { s_tile = (int)atomicAdd(prm.tile_counter, 1u); s_next = 0; }
         __syncthreads();
@@ -181,7 +182,7 @@ __global__ void __launch_bounds__(kRenderThreads, RT_MIN_BLOCKS) render_standard
         // mask, camera rays, shadow masks, shadow rays; rt_trace.cuh).  Scenes too large for the masks take groups from a
         // shared counter instead, so a warp that drew expensive samples traces fewer groups. ---
         const long long pix0 = tile * mt::kPixelsPerTile;
-        const bool lists = c_hdr.cull_words != 0;
+        constexpr bool lists = M;
 #pragma unroll 1
         for (int round = 0;; ++round) {
             int grp;
@@ -211,7 +212,7 @@ __global__ void __launch_bounds__(kRenderThreads, RT_MIN_BLOCKS) render_standard
             {   // with masks all threads of the CTA make these calls (barriers inside); a thread without a sample keeps company
                 const uint32_t* cand0 = lists ? camera_mask(active, d, cnt) : nullptr;
                 Hit ph; bool phit;
-                c = trace<C, K, F, RT_MAX_RECURSION>(active, lists, cand0, o, d, ph, phit, cnt);
+                c = trace<C, K, M, F, RT_MAX_RECURSION>(active, lists, cand0, o, d, ph, phit, cnt);
                 if (active && prm.ids) prm.ids[((long long)yy * nx + x) * 8 + (j & 7)] = phit ? ph.code : -1;
             }
 #pragma unroll
@@ -254,7 +255,7 @@ constexpr int kWaveTiles = RT_WAVE_TILES;
 __host__ __device__ __forceinline__ int wave_stride(int recursion) { return (2 + 3 * (recursion > 1 ? recursion : 1) + 7) & ~7; }
 constexpr int kWaveSamples = kWaveTiles * mt::kSamplesPerTile;
 
-template <bool C, bool K>
+template <bool C, bool K, bool M>
 __global__ void __launch_bounds__(kRenderThreads, RT_WAVE_BLOCKS) render_wavefront_kernel(RenderParams prm) {
     __shared__ uint32_t st[2][mt::kN];
     __shared__ __align__(16) uint32_t outw[mt::kOutputsPerTile];
@@ -272,7 +273,7 @@ __global__ void __launch_bounds__(kRenderThreads, RT_WAVE_BLOCKS) render_wavefro
     float4* my_state = prm.wave_state + (size_t)blockIdx.x * kWaveSamples * stride;
     Counters cnt = {0, 0, 0, 0};
     stage_scene<C>();
-    cand_init();
+    if (M) cand_init();
     for (;;) {
         // --- a batch: up to kWaveTiles tiles from the scheduler ---
         if (tid == 0) {
@@ -325,7 +326,7 @@ __global__ void __launch_bounds__(kRenderThreads, RT_WAVE_BLOCKS) render_wavefro
         int q = 0;
         // The first iteration traces the camera rays, in sample order: the CTA walks them in static rounds of 256 (32
         // neighbouring pixels) and builds the round's masks (rt_trace.cuh).  Later iterations have no such order.
-        bool camera_pass = c_hdr.cull_words != 0 && limit > 0;
+        bool camera_pass = M && limit > 0;
         for (;;) {                                                   // one ray of every unfinished sample per iteration
             const int n = s_count[q];
             if (n == 0) break;
@@ -371,10 +372,10 @@ __global__ void __launch_bounds__(kRenderThreads, RT_WAVE_BLOCKS) render_wavefro
                 RGBf c = rgb(0.f, 0.f, 0.f);
                 Hit ph; bool phit = false;
                 if (limit <= 0) {                                    // tracer.cpp:26: black, but the id buffer is still defined
-                    if (valid) { ++cnt.primary; if (prm.ids) phit = closest_hit<C, K>(o, d, 1e-4f, kInf, nullptr, ph, cnt); }
+                    if (valid) { ++cnt.primary; if (prm.ids) phit = closest_hit<C, K, false>(o, d, 1e-4f, kInf, nullptr, ph, cnt); }
                 } else {
                     const uint32_t* cand0 = camera_pass ? camera_mask(valid, d, cnt) : nullptr;
-                    more = !ray_step<C, K, false>(valid, camera_pass, cand0, o, d, depth, sp + 2, c, ph, phit, cnt) && valid;
+                    more = !ray_step<C, K, M, false>(valid, camera_pass, cand0, o, d, depth, sp + 2, c, ph, phit, cnt) && valid;
                 }
                 if (valid) {
                     if (primary && prm.ids) {
@@ -447,7 +448,7 @@ __device__ __host__ __forceinline__ bool paper_row_owned(int y, int rank, int wo
 #ifndef RT_PAPER_BLOCKS
 #define RT_PAPER_BLOCKS 3
 #endif
-template <bool C, bool K>
+template <bool C, bool K, bool M>
 __global__ void __launch_bounds__(256, RT_PAPER_BLOCKS) paper_gbuffer_kernel(GBuf* gb, int* ids, unsigned long long* counters, int rank, int world) {
     const int nx = c_hdr.nx, ny = c_hdr.ny;
     const long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -463,13 +464,13 @@ __global__ void __launch_bounds__(256, RT_PAPER_BLOCKS) paper_gbuffer_kernel(GBu
     V3 o, d; camera_ray(sx, sy, o, d);
     Hit h; h.mat = -1; h.t = 0.f; h.n = mk(0.f, 1.f, 0.f); h.front = true; h.code = -1;
     // the CTA's 256 pixels are one round: camera mask, centre rays, shadow masks, shadow rays (rt_trace.cuh)
-    const bool lists = c_hdr.cull_words != 0;
-    cand_init();
+    constexpr bool lists = M;
+    if (M) cand_init();
     const uint32_t* cand0 = lists ? camera_mask(need, d, cnt) : nullptr;
     bool hit = false;
-    if (need) { ++cnt.primary; hit = closest_hit<C, K>(o, d, 1e-4f, kInf, cand0, h, cnt); }      // tracer.cpp:111-120
+    if (need) { ++cnt.primary; hit = closest_hit<C, K, M>(o, d, 1e-4f, kInf, cand0, h, cnt); }      // tracer.cpp:111-120
     const bool lit = hit && own && h.mat >= 0;
-    const RGBf lum = shade<C, K>(lit, lists, h, madd(o, d, h.t), normalized(neg(d)), cnt);
+    const RGBf lum = shade<C, K, M>(lit, lists, h, madd(o, d, h.t), normalized(neg(d)), cnt);
     if (need) {
         GBuf g;
         g.hit = hit; g.t = hit ? h.t : kInf; g.mat = hit ? h.mat : -1; g.code = hit ? h.code : -1;
@@ -551,8 +552,8 @@ __global__ void __launch_bounds__(128) trace_rays_kernel(const double* rays, dou
     Counters cnt = {0, 0, 0, 0};
     Hit h; bool hit;
     if (!active) return;                         // (no barrier below: known-answer rays belong to no bundle)
-    const RGBf c = trace<C, K, false, RT_MAX_RECURSION>(true, false, nullptr, o, d, h, hit, cnt);
-    const bool occ = occluded<C, K>(o, d, 1e-3f, 5.0f, nullptr, cnt);
+    const RGBf c = trace<C, K, false, false, RT_MAX_RECURSION>(true, false, nullptr, o, d, h, hit, cnt);
+    const bool occ = occluded<C, K, false>(o, d, 1e-3f, 5.0f, nullptr, cnt);
     double* r = out + (size_t)i * 16;
     for (int k = 0; k < 16; ++k) r[k] = 0.0;
     r[0] = hit ? 1.0 : 0.0;

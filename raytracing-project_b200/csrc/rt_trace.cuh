@@ -197,17 +197,18 @@ __device__ __noinline__ ScanOut scan_shared(V3 o, V3 d, float tmin, float tmax, 
 #ifndef RT_SCAN_SHARED
 #define RT_SCAN_SHARED 0          // A/B: 1 = the out-of-line scan for every scene
 #endif
-template <bool C, bool K, bool ANY>
+// M: the kernel was built with round-level masks (rt_device.cuh); kernels without them contain none of that code.
+template <bool C, bool K, bool M, bool ANY>
 __device__ __forceinline__ void scan(V3 o, V3 d, float tmin, float tmax, const uint32_t* cand, ScanResult& res, Counters& cnt) {
-    if (cand) scan_masked<C, K>(o, d, tmin, tmax, ANY, cand, res, cnt.tests);
+    if (M && cand) scan_masked<C, K>(o, d, tmin, tmax, ANY, cand, res, cnt.tests);
     else if (K || RT_SCAN_SHARED) { const ScanOut so = scan_shared<C, K>(o, d, tmin, tmax, ANY); res = so.r; cnt.tests += so.tests; }
     else scan_body<C, K>(o, d, tmin, tmax, ANY, res, cnt.tests);
 }
 
-template <bool C, bool K>
+template <bool C, bool K, bool M>
 __device__ __forceinline__ bool closest_hit(V3 o, V3 d, float tmin, float tmax, const uint32_t* cand, Hit& hit, Counters& cnt) {
     ScanResult sr;
-    scan<C, K, false>(o, d, tmin, tmax, cand, sr, cnt);
+    scan<C, K, M, false>(o, d, tmin, tmax, cand, sr, cnt);
     const int best = sr.best;
     if (best < 0) return false;
     // ---- finalise the winner: normal, front_face, material, id code ----
@@ -247,10 +248,10 @@ __device__ __forceinline__ bool closest_hit(V3 o, V3 d, float tmin, float tmax, 
     return true;
 }
 
-template <bool C, bool K>
+template <bool C, bool K, bool M>
 __device__ __forceinline__ bool occluded(V3 o, V3 d, float tmin, float tmax, const uint32_t* cand, Counters& cnt) {
     ScanResult sr;
-    scan<C, K, true>(o, d, tmin, tmax, cand, sr, cnt);
+    scan<C, K, M, true>(o, d, tmin, tmax, cand, sr, cnt);
     return sr.best >= 0;
 }
 
@@ -306,12 +307,12 @@ __device__ __forceinline__ void light_shade(int l, const float4 m0, float ks, fl
 // shadow-ray origins and culls the scene against the bundle towards every light (cand_build, two barriers), and the shadow
 // scans take their candidates from those masks.  Without LISTS (secondary rays, known-answer rays) the scans use the
 // per-lane mask only and the call may come from divergent code.
-template <bool C, bool K>
+template <bool C, bool K, bool M>
 __device__ __forceinline__ RGBf shade(bool lit, const bool LISTS, const Hit& h, V3 p, V3 wo, Counters& cnt) {
     const float eps = fmaxf(1e-3f, 1e-4f * h.t);                             // shading.cpp:43
     const V3 so = madd(p, h.n, eps);
     const int nl = c_hdr.n_lights;
-    const bool lists = LISTS && c_hdr.cull_words != 0;
+    const bool lists = M && LISTS;
     if (lists) {
         CandShared* S = cand_shared();
         cand_box_add(lit, so, S->org_lo, S->org_hi, &S->nan_flags, 2);
@@ -336,7 +337,7 @@ __device__ __forceinline__ RGBf shade(bool lit, const bool LISTS, const Hit& h, 
             if (tmaxS <= eps) continue;                                      // shading.cpp:98
             ++cnt.shadow;
             const uint32_t* cand = lists ? cand_of(1 + l0 + k) : nullptr;
-            if (!occluded<C, K>(so, normalized(wi), eps, tmaxS, cand, cnt)) vis |= 1u << k;   // Ray ctor re-normalises (core.h:278)
+            if (!occluded<C, K, M>(so, normalized(wi), eps, tmaxS, cand, cnt)) vis |= 1u << k;   // Ray ctor re-normalises (core.h:278)
         }
         const float4 m0 = material(h.mat, 0), m2 = material(h.mat, 2);
         while (vis) {
@@ -359,21 +360,21 @@ __device__ __forceinline__ RGBf shade(bool lit, const bool LISTS, const Hit& h, 
 // (o, d, sp) is its next ray.  FLAT: no ray of the scene can spawn a child (no reflective / refractive material, or
 // recursion == 1): no frames are touched and every tree finishes with its first ray.  LISTS: the ray is a camera ray of
 // a round — `cand` is the round's mask of the camera bundle, ALL threads of the CTA make the call (see shade).
-template <bool C, bool K, bool FLAT>
+template <bool C, bool K, bool M, bool FLAT>
 __device__ __forceinline__ bool ray_step(bool alive, const bool LISTS, const uint32_t* cand, V3& o, V3& d, int& sp, float4* __restrict__ frames,
                                          RGBf& result, Hit& primary, bool& primary_hit, Counters& cnt) {
     const int limit = c_hdr.recursion;
     Hit h; h.mat = -1; h.t = 0.f; h.n = mk(0.f, 1.f, 0.f); h.front = true; h.code = -1;
     bool hit = false;
     if (alive) {
-        hit = closest_hit<C, K>(o, d, 1e-4f, kInf, cand, h, cnt);          // tracer.cpp:29
+        hit = closest_hit<C, K, M>(o, d, 1e-4f, kInf, cand, h, cnt);       // tracer.cpp:29
         if (FLAT || LISTS || sp == 0) { ++cnt.primary; primary = h; primary_hit = hit; } else ++cnt.secondary;
     }
     const V3 p = madd(o, d, h.t);
     const V3 wo = normalized(neg(d));
     const bool lit = hit && h.mat >= 0;
     if (!LISTS && !alive) return true;
-    const RGBf total = shade<C, K>(lit, LISTS, h, p, wo, cnt);              // tracer.cpp:31
+    const RGBf total = shade<C, K, M>(lit, LISTS, h, p, wo, cnt);           // tracer.cpp:31
     if (!alive) return true;
     if (!hit) result = rgb(c_hdr.bg[0], c_hdr.bg[1], c_hdr.bg[2]);          // tracer.cpp:72
     else if (!lit) result = rgb(1.f, 0.f, 1.f);                              // shading.cpp:33
@@ -441,24 +442,24 @@ __device__ __forceinline__ bool ray_step(bool alive, const bool LISTS, const uin
 // Tracer::trace (tracer.cpp:12-20) for one sample per thread.  `active` false: the thread has no sample.  D = frames
 // available = deepest recursion served.  LISTS: the sample is a camera ray of a round whose camera-bundle mask is `cand`;
 // ALL threads of the CTA make the call (the first ray and its shadow rays use the round's masks, deeper rays none).
-template <bool C, bool K, bool FLAT, int D>
+template <bool C, bool K, bool M, bool FLAT, int D>
 __device__ __forceinline__ RGBf trace(bool active, const bool LISTS, const uint32_t* cand, V3 o, V3 d, Hit& primary, bool& primary_hit, Counters& cnt) {
     primary_hit = false;
     RGBf result = rgb(0.f, 0.f, 0.f);
     if (c_hdr.recursion <= 0) {                                              // tracer.cpp:26 at depth 0: black, ids still defined
-        if (active) { ++cnt.primary; primary_hit = closest_hit<C, K>(o, d, 1e-4f, kInf, cand, primary, cnt); }
+        if (active) { ++cnt.primary; primary_hit = closest_hit<C, K, M>(o, d, 1e-4f, kInf, cand, primary, cnt); }
         return result;
     }
     if (FLAT) {
         int sp = 0;
-        ray_step<C, K, true>(active, LISTS, cand, o, d, sp, nullptr, result, primary, primary_hit, cnt);
+        ray_step<C, K, M, true>(active, LISTS, cand, o, d, sp, nullptr, result, primary, primary_hit, cnt);
         return result;
     }
     float4 frames[3 * D];
     int sp = 0;                     // == depth of the ray being traced
     bool lists = LISTS;             // the camera ray: all threads; deeper rays: the threads whose tree goes on, no masks
     for (;;) {
-        const bool done = ray_step<C, K, false>(active, lists, lists ? cand : nullptr, o, d, sp, frames, result, primary, primary_hit, cnt);
+        const bool done = ray_step<C, K, M, false>(active, lists, lists ? cand : nullptr, o, d, sp, frames, result, primary, primary_hit, cnt);
         if (!active || done) break;
         lists = false;
     }
