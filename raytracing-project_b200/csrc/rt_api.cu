@@ -392,9 +392,10 @@ int rt_scene_upload(const rt_scene_desc* d, rt_scene** out) {
     // Scenes whose table is too long for a CTA to cull per round (> kMaxCullWords x 32 entries) scan without masks.
     // Round-level masks pay when a scan is more than a handful of tests and the table is short enough for a CTA to cull per
     // round: not for scenes of a few primitives (pokeballs: 4 objects), not for clustered scenes (their scans already walk a
-    // spatial structure; culling 1 300 entries per bundle and round cost more than it saved: synthetic-A 2K 23.8 -> 41 ms).
+    // spatial structure; culling 1 300 entries per bundle and round cost more than it saved: synthetic-A 2K 23.8 -> 41 ms),
+    // not for the wavefront kernel (only its camera pass could use them: synthetic-B 1K 32.1 -> 37.3 ms).
     constexpr int kMaxCullWords = 8, kMinCullEntries = 10;
-    bool cull = s->cull_words > 0 && s->cull_words <= kMaxCullWords && !s->clustered && d->n_objects + d->n_leaves >= kMinCullEntries;
+    bool cull = s->cull_words > 0 && s->cull_words <= kMaxCullWords && !s->clustered && !s->bounces && d->n_objects + d->n_leaves >= kMinCullEntries;
     if (g_opts.cull == 0) cull = false;
     if (g_opts.cull == 1) cull = s->cull_words > 0 && s->cull_words <= 96 && !s->clustered;        // test hook: masks wherever they can be built
     h.cull_geom = s->d_cull_geom; h.cull_words = cull ? s->cull_words : 0; h.cull_plane_bits = s->d_cull_plane_bits; h.cull_leaf_word = s->cull_leaf_word;

@@ -233,7 +233,8 @@ __device__ __forceinline__ void cand_build(int b0, int nb, unsigned& tests) {
             Sphere4 q; q.x = g.x; q.y = g.y; q.z = g.z; q.w = g.w;
             // padding entries have w < 0; CSG leaves (words from cull_leaf_word on) are culled on the whole line
             // (a bundle too wide to cull — a round across a silhouette, a light inside the box — keeps every entry)
-            const bool cand = B.wide ? !(g.w < 0.f) : plane ? !bundle_rejects_plane(B, q) : (g.w >= 0.f && !bundle_rejects(B, q, B.t_hi, w < c_hdr.cull_leaf_word));
+            // (a plane's w is its offset n.p0 and may well be negative: only non-plane entries use w < 0 as "padding")
+            const bool cand = plane ? (B.wide || !bundle_rejects_plane(B, q)) : (g.w >= 0.f && (B.wide || !bundle_rejects(B, q, B.t_hi, w < c_hdr.cull_leaf_word)));
             ++tests;
             const uint32_t bits = __ballot_sync(kFullWarp, cand);
             if (lane == 0) cand_words(b)[w] = bits;
@@ -241,7 +242,8 @@ __device__ __forceinline__ void cand_build(int b0, int nb, unsigned& tests) {
     } else if (nan) {                                             // a NaN among the rays: keep every entry
         for (int k = threadIdx.x >> 5; k < nb * W; k += nwarps) {
             const int bb = k / W, w = k - bb * W;
-            const uint32_t bits = __ballot_sync(kFullWarp, !(__ldg(c_hdr.cull_geom + 32 * w + lane).w < 0.f));
+            const bool plane = (__ldg(c_hdr.cull_plane_bits + w) >> lane) & 1u;
+            const uint32_t bits = __ballot_sync(kFullWarp, plane || !(__ldg(c_hdr.cull_geom + 32 * w + lane).w < 0.f));
             if (lane == 0) cand_words(b0 + bb)[w] = bits;
         }
     }

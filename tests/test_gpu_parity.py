@@ -174,7 +174,7 @@ def test_flat_kernel_and_generic_loop_agree(gpu, name, force):
     forced back onto the generic loop (flat = 0), and with the round-level culling switched off (cull = 0: every ray scans
     every run, as in the reference), frame, ids and ray counts must not change by a bit."""
     out = []
-    for env in ({"flat": 0}, {"cull": 0}, {"flat": 0, "cull": 0}, {}):
+    for env in ({"flat": 0}, {"cull": 0}, {"flat": 0, "cull": 0}, {"cull": 1}, {}):
         for k in ("flat", "cull"):
             force(k, -1)
         for k, v in env.items():
@@ -188,16 +188,19 @@ def test_flat_kernel_and_generic_loop_agree(gpu, name, force):
             assert np.array_equal(out[0][0][k], got[k]), k
         for k in ("primary_rays", "shadow_rays", "secondary_rays"):
             assert out[0][1][k] == st[k], k
-    assert out[3][1]["prim_tests"] < out[1][1]["prim_tests"], "the round-level culling must save primitive tests"
+    assert out[3][1]["prim_tests"] <= out[1][1]["prim_tests"]
+    if name in ("snorlax_small", "pokeballs_small", "penguin_small"):
+        assert out[3][1]["prim_tests"] < out[1][1]["prim_tests"], "the round-level culling must save primitive tests"
 
 
-@pytest.mark.parametrize("name", ["quirks", "synthetic_b_small", "synthetic_a_small", "quirks_far", "big_floor"])
+@pytest.mark.parametrize("name", ["quirks", "synthetic_b_small", "synthetic_a_small", "quirks_far", "big_floor", "snorlax_4k_small",
+                                  "snorlax_4k_reflect_small", "penguin_small", "pokeballs_small"])
 def test_culling_does_not_change_a_bit(gpu, name, force):
     """Round-level culling (candidate masks per 32 pixels and per light) against the plain scans: frame, ids and ray counts
     identical, in standard and in paper mode, on the bounce-heavy and the clustered scenes as well."""
     out = {}
     for cull in (0, 1):
-        force("cull", cull)
+        force("cull", cull)                  # 1: masks wherever they can be built (also where the library would not choose them)
         sc = gpu.load_scene_from_json(scene_path(name))
         for mode in ("standard", "paper"):
             out[cull, mode], tr = render_gpu(gpu, sc, mode)
