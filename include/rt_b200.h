@@ -191,6 +191,22 @@ int rt_render_device(rt_scene*, int mode, int rank, int world,
                      void* rgba8_device, void* rgbf_device, void* ids_device,
                      void* stream, rt_stats* stats);
 
+/* Paper-mode frame (RT_MODE_PAPER) for callers that cannot allocate: code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc.  This entry point has NO counterpart in the reference.
+ * Same pixels as rt_render_device(scene, RT_MODE_PAPER, rank, world, rgba8_device,
+ * NULL, NULL, stream, NULL), but the G-buffer between the two passes lives in a file-scope static __device__ array
+ * instead of a grown cudaMalloc buffer, and the call itself performs no cudaMalloc / cudaFree / allocating library call.
+ *   - limit: width * height <= RT_NOALLOC_MAX_PIXELS (1280 x 1024; 32 B of G-buffer per pixel + 256 B of counters =
+ *     40 MiB of device memory held by every GPU that loads the library, until the process exits); larger frames are
+ *     rejected with RT_ERR_LIMIT and a message naming the limit;
+ *   - rt_init and rt_scene_upload (which do allocate) must have been called before; rgba8_device is the caller's
+ *     H*W uchar4 buffer; stream as in rt_render_device; asynchronous: order your reads after `stream`;
+ *   - every call on a device shares the one scratch array (and, like every render call, the constant scene header):
+ *     calls that overlap on the GPU, on different streams, race.  The counters are cleared by every call; the
+ *     G-buffer keeps the previous call's contents and needs no clearing (pass 1 writes every entry pass 2 reads). */
+#define RT_NOALLOC_MAX_PIXELS (1280 * 1024)
+int rt_render_paper_device_noalloc(rt_scene*, int rank, int world, void* rgba8_device, void* stream);
+
 /* ---- peer frame (multi-GPU, one process per GPU) ---------------------------------------------------
  * The reference writes one std::vector<Color> (tracer.cpp:250,297); with several GPUs the ranks write their
  * tiles straight into ONE RGBA8 frame that lives on rank 0, over NVLink peer memory, so the render kernel's

@@ -26,6 +26,7 @@ LIB_PATH = os.path.join(_HERE, "librt_b200.so")
 RAY_CLI = os.path.join(_HERE, "ray")
 TILE_PIXELS = 156
 PAPER_ROWS = 16
+NOALLOC_MAX_PIXELS = 1280 * 1024     # RT_NOALLOC_MAX_PIXELS
 
 
 class RtError(RuntimeError):
@@ -95,7 +96,7 @@ ABI_SYMBOLS = [
     "rt_init", "rt_shutdown", "rt_last_error", "rt_version",
     "rt_compile_json_text", "rt_compile_json_file", "rt_compiled_desc", "rt_compiled_free", "rt_compiled_add_dir_light",
     "rt_scene_upload", "rt_scene_free", "rt_scene_size",
-    "rt_render", "rt_render_device", "rt_trace_rays", "rt_debug_jitter", "rt_debug_mt_block_host", "rt_debug_mt_jump_host", "rt_debug_device_layout", "rt_debug_mask_table", "rt_debug_set_option",
+    "rt_render", "rt_render_device", "rt_render_paper_device_noalloc", "rt_trace_rays", "rt_debug_jitter", "rt_debug_mt_block_host", "rt_debug_mt_jump_host", "rt_debug_device_layout", "rt_debug_mask_table", "rt_debug_set_option",
     "rt_measure_fp32_peak",
     "rt_write_png_rgb8",
     "rt_peer_frame_create", "rt_peer_frame_open", "rt_peer_frame_close",
@@ -131,6 +132,7 @@ def lib():
         L.rt_render.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(RtStats)]
         L.rt_render_device.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                        C.c_void_p, C.POINTER(RtStats)]
+        L.rt_render_paper_device_noalloc.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         L.rt_trace_rays.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         L.rt_debug_jitter.argtypes = [C.c_uint64, C.c_int, C.c_void_p]
         L.rt_debug_mt_block_host.argtypes = [C.c_uint32, C.c_uint64, C.c_void_p]
@@ -277,6 +279,13 @@ class Tracer:
         if want_stats:
             self.last_stats = st.as_dict()
         return self.last_stats
+
+    def render_paper_device_noalloc(self, rgba8_ptr: int, stream: int | None = None, rank: int = 0, world: int = 1) -> None:
+        """Paper frame into a caller-owned DEVICE buffer through the entry point that allocates nothing
+        (rt_render_paper_device_noalloc: G-buffer in a static device array, at most NOALLOC_MAX_PIXELS pixels)."""
+        if stream is not None and stream == 0:
+            stream = 1          # cudaStreamLegacy, as in render_device
+        _check(lib().rt_render_paper_device_noalloc(self.scene.device_handle(), rank, world, C.c_void_p(rgba8_ptr), C.c_void_p(stream or None)))
 
     def trace_rays(self, rays: np.ndarray) -> np.ndarray:
         """Known-answer entry point: [n,6] float64 rays -> [n,16] float64 records (see rt_b200.h)."""

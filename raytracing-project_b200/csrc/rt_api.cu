@@ -666,6 +666,64 @@ int rt_render_device(rt_scene* s, int mode, int rank, int world, void* rgba8_dev
     return RT_OK;
 }
 
+}  // extern "C"
+
+// ---- Paper frame without any allocation (rt_render_paper_device_noalloc) ----------------------------------------
+// Scratch of the entry point below: 256 bytes of device counters (cleared by every call), then the G-buffer of
+// paper_gbuffer_kernel / paper_post_kernel for at most RT_NOALLOC_MAX_PIXELS pixels.  The array lives in the module's
+// global segment of every device that loads the library (40 MiB, until the process exits).  In host code the name below
+// is only a stand-in for the symbol: the device address comes from cudaGetSymbolAddress, once per device.
+static constexpr size_t kNoAllocHead = 256;
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocHead + (size_t)RT_NOALLOC_MAX_PIXELS * sizeof(rtd::GBuf)];
+static constexpr int kNoAllocMaxDevices = 64;
+static unsigned char* g_noalloc_ptr[kNoAllocMaxDevices] = {};      // device address of g_noalloc_scratch, per device ordinal
+
+namespace {
+// Set-up, once per device, with that device current (the caller holds g_ctx.mu and has called cudaSetDevice).
+int noalloc_scratch(int device, unsigned char** out) {
+    if (device < 0 || device >= kNoAllocMaxDevices) return fail(RT_ERR_LIMIT, "rt_render_paper_device_noalloc: device ordinal beyond 63");
+    if (!g_noalloc_ptr[device]) {
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p) return fail(RT_ERR_CUDA, std::string("cudaGetSymbolAddress(g_noalloc_scratch): ") + cudaGetErrorString(e));
+        g_noalloc_ptr[device] = (unsigned char*)p;
+    }
+    *out = g_noalloc_ptr[device];
+    return RT_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int rt_render_paper_device_noalloc(rt_scene* s, int rank, int world, void* rgba8_device, void* stream) {
+    int rc = check_args(s, RT_MODE_PAPER, rank, world); if (rc) return rc;
+    if (!rgba8_device) return fail(RT_ERR_ARG, "rt_render_paper_device_noalloc: rgba8_device is required");
+    const long long npx = (long long)s->width * s->height;
+    if (npx > (long long)RT_NOALLOC_MAX_PIXELS)
+        return fail(RT_ERR_LIMIT, "rt_render_paper_device_noalloc: " + std::to_string(s->width) + "x" + std::to_string(s->height) + " = " + std::to_string(npx) +
+                                  " pixels exceed the static scratch of RT_NOALLOC_MAX_PIXELS = " + std::to_string((long long)RT_NOALLOC_MAX_PIXELS) +
+                                  " pixels; use rt_render_device");
+    std::lock_guard<std::mutex> lk(g_ctx.mu);
+    CU(cudaSetDevice(g_ctx.device));
+    unsigned char* scratch = nullptr;
+    rc = noalloc_scratch(g_ctx.device, &scratch); if (rc) return rc;
+    auto* counters = (unsigned long long*)scratch;
+    auto* gbuf = (rtd::GBuf*)(scratch + kNoAllocHead);
+    cudaStream_t st = stream ? (cudaStream_t)stream : g_ctx.stream;
+    rc = bind_scene(s, st); if (rc) return rc;
+    // the counters must start at zero; the G-buffer need not: pass 1 writes every entry pass 2 reads (own rows + halo)
+    CU(cudaMemsetAsync(counters, 0, kNoAllocHead, st));
+    const unsigned blocks = (unsigned)((npx + 255) / 256);
+    const bool mm = s->hdr.cull_words != 0;
+    auto paper = s->clustered ? (s->fits_const ? rtd::paper_gbuffer_kernel<true, true, false> : rtd::paper_gbuffer_kernel<false, true, false>)
+               : s->fits_const ? (mm ? rtd::paper_gbuffer_kernel<true, false, true> : rtd::paper_gbuffer_kernel<true, false, false>)
+                               : (mm ? rtd::paper_gbuffer_kernel<false, false, true> : rtd::paper_gbuffer_kernel<false, false, false>);
+    paper<<<blocks, 256, s->smem_bytes, st>>>(gbuf, nullptr, counters, rank, world);
+    rtd::paper_post_kernel<<<blocks, 256, 0, st>>>(gbuf, (uchar4*)rgba8_device, nullptr, s->width, s->height, rank, world);
+    CU(cudaGetLastError());
+    return RT_OK;
+}
+
 int rt_peer_frame_create(size_t bytes, void** device_ptr, unsigned char handle[RT_IPC_HANDLE_BYTES]) {
     static_assert(sizeof(cudaIpcMemHandle_t) == RT_IPC_HANDLE_BYTES, "IPC handle size");
     if (!device_ptr || !handle || bytes == 0) return fail(RT_ERR_ARG, "rt_peer_frame_create: null argument or zero size");
