@@ -7,8 +7,10 @@
 
 A "step" is one frame of the workload scene (default scenes/snorlax_4k.json: snorlax at 3840x2160,
 recursion 5, 5 point lights — configs[2], the configuration the metric and the 1,000x target are quoted on).
-`value` = rays/s with the scene resident on the device (kernel + NCCL gather, CUDA events, max over ranks);
-`e2e`   = the same through the C-ABI call with HOST buffers (scene upload + render + D2H of the RGB8 frame).
+`value` = rays/s with the scene resident on the device (kernel + pixel exchange, CUDA events, max over ranks);
+`e2e`   = the same through the C-ABI call rt_render with HOST buffers: JSON parse + scene compile + upload (H2D) + render,
+          the RGB8 frame leaving the GPU(s) inside the kernel's own stores into one pinned host frame (D2H over every
+          rank's own PCIe link; rt_b200.h "host-direct output"), wall clock around the call + the ranks' barrier.
 Rays = every Scene::intersect-equivalent and Scene::occluded-equivalent query (primary + shadow +
 reflection + refraction), counted on the device; the CPU legs count the same queries with the oracle.
 """
@@ -306,6 +308,17 @@ def run_ours(args) -> None:
         dist.all_reduce(cnt)
     tot = dict(zip(keys, [int(v) for v in cnt.tolist()]))
     rays_per_frame = tot["primary_rays"] + tot["shadow_rays"] + tot["secondary_rays"]
+    # Algorithmic work of the frame = the primitive tests of the reference's linear scans (scene.cpp:10-42), counted by the
+    # same kernels with the round-level culling switched off (one untimed frame); what the culled kernels execute is less.
+    rt.debug_option("cull", 0)
+    scene_lin = rt.load_scene_from_json(args.scene)
+    st_lin = dict(rt.Tracer(scene_lin, mode).render_device(target, stream=stream, rank=rank, world=world, want_stats=True))
+    rt.debug_option("cull", -1)
+    torch.cuda.synchronize(); scene_lin.close()
+    lin = torch.tensor([st_lin["prim_tests"]], dtype=torch.int64, device=dev)
+    if world > 1:
+        dist.all_reduce(lin)
+    tests_linear = int(lin.item())
     peak_tflops = rt.measure_fp32_peak()
 
     for _ in range(max(args.warmup, 3)):
@@ -333,17 +346,46 @@ def run_ours(args) -> None:
     ms_per_step = float(t[0]) / args.steps
     kernel_ms = float(t[1]) / args.steps
 
-    # ---- end to end through the C ABI with host buffers: scene upload (H2D) + render + D2H of the frame ----
-    host = torch.empty((H, W, 3), dtype=torch.uint8).pin_memory() if world == 1 else torch.empty((H, W, 4), dtype=torch.uint8).pin_memory()
+    # ---- end to end through the C ABI with host buffers: parse + compile + upload (H2D) + render + the frame in HOST memory ----
+    # The host frame is pinned, device-mapped memory (N = 1: a pinned torch tensor; N > 1: ONE POSIX-shm frame every rank
+    # maps, rt_host_frame_*): rt_render's kernel stores the packed RGB8 pixels straight into it, every rank over its own
+    # PCIe link, and the step ends with the ranks' barrier.  Fallback (no /dev/shm): peer frame + one D2H copy on rank 0.
+    shared = None; e2e_path = "rt_render -> pinned host tensor (host-direct stores)"
+    if world > 1:
+        name = "/rt_b200_%s_%d" % (os.environ.get("MASTER_PORT", "0"), os.getppid())
+        ok = torch.ones(1, dtype=torch.int32, device=dev)
+        try:
+            if rank == 0:
+                shared = rt.HostFrame(H, W, name=name, create=True)
+        except Exception as e:      # noqa: BLE001
+            print("bench.py: shared host frame unavailable (%s)" % e, file=sys.stderr); ok.zero_()
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if int(ok.item()) and rank != 0:
+            try:
+                shared = rt.HostFrame(H, W, name=name, create=False)
+            except Exception as e:  # noqa: BLE001
+                print("bench.py: rank %d cannot map the shared host frame (%s)" % (rank, e), file=sys.stderr); ok.zero_()
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if not int(ok.item()):
+            if shared is not None:
+                shared.close()
+            shared = None
+        e2e_path = ("rt_render(rank, world) on every rank -> ONE shared pinned host frame (host-direct stores) + barrier" if shared is not None
+                    else "rt_render_device -> peer frame on rank 0 -> one D2H copy")
+    host = None
+    if shared is None:
+        host = torch.empty((H, W, 3), dtype=torch.uint8).pin_memory() if world == 1 else torch.empty((H, W, 4), dtype=torch.uint8).pin_memory()
     d = scene.desc
     h2d = (d.n_objects + d.n_leaves) * 32 + d.n_pokeballs * 48 + d.n_affines * 48 + d.n_ops * 4 + d.n_materials * 48 + d.n_lights * 32 + 256
     def e2e_step():
         s2 = rt.load_scene_from_json(args.scene)                         # parse + compile on the host, upload below
-        t2 = rt.Tracer(s2, mode)
-        if world == 1:
-            st2 = rt.RtStats()
-            rt._check(rt.lib().rt_render(s2.device_handle(), int(mode), 0, 1, C.c_void_p(host.data_ptr()), None, None, C.byref(st2)))
+        if world == 1 or shared is not None:
+            dst = host.data_ptr() if shared is None else shared.ptr
+            rt._check(rt.lib().rt_render(s2.device_handle(), int(mode), rank, world, C.c_void_p(dst), None, None, None))
+            if world > 1:
+                dist.barrier()
         else:
+            t2 = rt.Tracer(s2, mode)
             t2.render_device(target, stream=stream, rank=rank, world=world)
             full = finish()
             if rank == 0:
@@ -360,6 +402,7 @@ def run_ours(args) -> None:
     if world > 1:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_ms = float(te[0])
+    d2h_bytes = W * H * (3 if (world == 1 or shared is not None) else 4)
 
     # ---- N > 1: the peer-assembled frame must equal the frame one GPU renders alone, byte for byte (untimed) ----
     frame_equal = None
@@ -371,10 +414,18 @@ def run_ours(args) -> None:
             tracer.render_device(alone.data_ptr(), stream=stream, rank=0, world=1)
             torch.cuda.synchronize()
             frame_equal = bool(torch.equal(assembled.reshape(H, W, 4), alone))
+            if shared is not None:      # ... and so must the frame the e2e leg assembled in host memory
+                frame_equal = frame_equal and bool(np.array_equal(shared.array, alone[..., :3].cpu().numpy()))
         barrier()
+    elif host is not None:
+        alone = torch.zeros((H, W, 4), dtype=torch.uint8, device=dev)
+        tracer.render_device(alone.data_ptr(), stream=stream, rank=0, world=1)
+        torch.cuda.synchronize()
+        frame_equal = bool(np.array_equal(host.numpy(), alone[..., :3].cpu().numpy()))     # host-direct frame == device frame
 
     if rank == 0:
-        flops = flops_of(tot, W * H)
+        flops_exec = flops_of(tot, W * H)
+        flops = flops_of(dict(tot, prim_tests=max(tests_linear, tot["prim_tests"])), W * H)
         achieved = flops / (kernel_ms * 1e-3) / 1e12 / world          # per GPU
         line = {
             "metric": "Mrays/s", "value": rays_per_frame / (ms_per_step * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world,
@@ -386,7 +437,7 @@ def run_ours(args) -> None:
                        "l2": "flushed between timed steps (256 MB memset)"},
             "rays_per_frame": rays_per_frame, "rays": tot, "kernel_ms": kernel_ms,
             "e2e": {"value": rays_per_frame / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_frame": e2e_ms,
-                    "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(W * H * (3 if world == 1 else 4))},
+                    "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h_bytes), "path": e2e_path},
             "gpu_launches": args.steps * (2 if args.paper else 1) * world,
             # north_star: this path is FP32 CUDA-core work, reported against the FP32 roofline.  MEASURED_PEAKS.json holds
             # only HBM and bf16-tensor peaks, so the denominator is measured live on this GPU (FFMA micro-benchmark).
@@ -394,12 +445,17 @@ def run_ours(args) -> None:
                          "traffic": traffic_of(os.path.basename(args.scene), args.paper),
                          "peak_source": "measured live (dependent-free FFMA micro-benchmark, rt_measure_fp32_peak)",
                          "flops_per_frame": flops,
+                         "flops_note": "algorithmic = 17 x the primitive tests of the reference's linear scans (same kernels with "
+                                       "round-level culling off, one untimed frame) + 80/shadow ray + 30/closest hit + 12/pixel; "
+                                       "flops_executed_per_frame counts the tests the culled kernels really ran",
+                         "prim_tests_linear_scan": tests_linear, "flops_executed_per_frame": flops_exec,
+                         "achieved_executed": flops_exec / (kernel_ms * 1e-3) / 1e12 / world,
                          "framebuffer": {"bytes_per_frame": int(W * H * 4), "achieved_gbs": W * H * 4 / (kernel_ms * 1e-3) / 1e9 / world,
                                          "hbm_peak_gbs": hbm_peak_gbs(), "note": "RGBA8 stores only; the frame is compute-bound"}},
             "clocks": clocks,
         }
         if frame_equal is not None:
-            line["frame_equals_single_gpu"] = frame_equal
+            line["frame_equals_single_gpu" if world > 1 else "host_frame_equals_device_frame"] = frame_equal
         if world == 1 and not args.no_cpu:
             try:
                 if args.paper:
@@ -415,6 +471,9 @@ def run_ours(args) -> None:
             except Exception as e:  # the baseline is a report, never a reason to lose the GPU number
                 line["cpu_baseline"] = {"error": str(e)}
         print(json.dumps(line))
+    if shared is not None:
+        barrier()
+        shared.close()
     if peer is not None:
         peer.close()
     if world > 1:

@@ -151,6 +151,11 @@ typedef struct rt_stats {
 /* ---- library / device ---------------------------------------------------------------------- */
 /* Select the CUDA device this process renders on (one process per GPU).  device < 0: current. */
 int rt_init(int device);
+/* Contexts on several devices of one box for rt_render_multi (devices = NULL: 0 .. n_devices - 1); the first becomes the
+ * process's render device when rt_init has not chosen one.  The reference is single-threaded CPU code (main.cpp:42-94):
+ * nothing to replace; SURVEY.md section 5 asks for the GPU list to come from the environment (RAY_GPUS, csrc/ray_main.cpp). */
+int rt_init_devices(const int* devices, int n_devices);
+/* Releases every device resource of the library; scenes uploaded before become invalid (rt_scene_free stays legal). */
 void rt_shutdown(void);
 const char* rt_last_error(void);
 const char* rt_version(void);
@@ -184,9 +189,31 @@ int rt_scene_size(const rt_scene*, int* width, int* height);
 int rt_render(rt_scene*, int mode, int rank, int world,
               uint8_t* rgb8, float* rgbf, int32_t* ids, rt_stats* stats);
 
+/* Host-direct output.  When `rgb8` of rt_render is pinned host memory that is mapped into the device's address space
+ * (rt_host_frame_alloc / rt_host_frame_open below, cudaHostAlloc, cudaHostRegister(..Mapped)) the render kernel stores the
+ * packed R,G,B bytes straight into it, tile by tile as aligned 128-byte PCIe writes, while the other tiles are still being
+ * traced: no device frame, no pack pass, no copy afterwards — this is framebuffer_to_mat_bgr8 (main.cpp:19-34) fused into
+ * the kernel's own store.  With world > 1 the pixels of other ranks are left untouched, so several GPUs — one process each
+ * (same shm_name) or all in one process (rt_render_multi) — fill ONE frame, each over its own PCIe link.
+ *   rt_host_frame_alloc(bytes, NULL, &p)      private pinned + mapped host memory
+ *   rt_host_frame_alloc(bytes, "/name", &p)   the same, backed by POSIX shared memory that other processes open with
+ *   rt_host_frame_open("/name", bytes, &p)    (every process registers the mapping with its own CUDA context)
+ *   rt_host_frame_free(p)                     waits for the devices, unmaps; the creator also unlinks the name            */
+int rt_host_frame_alloc(size_t bytes, const char* shm_name, void** host_ptr);
+int rt_host_frame_open(const char* shm_name, size_t bytes, void** host_ptr);
+int rt_host_frame_free(void* host_ptr);
+
+/* Tracer::render (tracer.cpp:247-305) on n_devices GPUs of one box from ONE process: device i renders tiles i, i + n, ...
+ * of a replica of the scene and stores its pixels into `rgb8` (H*W*3, row 0 = top) — directly when rgb8 is a host frame,
+ * else through a pinned frame of the library that is copied out at the end.  No peer access, no collective.
+ * stats (optional): counters summed over the devices, kernel_ms = the slowest device.                                 */
+int rt_render_multi(const rt_scene_desc* desc, int mode, const int* devices, int n_devices, uint8_t* rgb8, rt_stats* stats);
+
 /* Same, but the frame stays on the device: rgba8_device is H*W uchar4 (A = 255), rgbf_device is
  * H*W float4 (may be NULL), ids_device H*W*S int32 (may be NULL).  `stream` is a cudaStream_t
- * (NULL = the library's stream).  Used by the multi-GPU harness, which gathers the slices with NCCL. */
+ * (NULL = the library's stream).  Asynchronous unless stats is given.  ONE frame is in flight per device: the tile
+ * counter, the ray counters, the scratch buffers and the constant scene header are per device, so a call on another
+ * stream first waits (cudaStreamWaitEvent) for the previous frame of that device; calls are serialised by a mutex. */
 int rt_render_device(rt_scene*, int mode, int rank, int world,
                      void* rgba8_device, void* rgbf_device, void* ids_device,
                      void* stream, rt_stats* stats);

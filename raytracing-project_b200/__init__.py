@@ -93,7 +93,8 @@ class RtSceneDesc(C.Structure):
 
 # every symbol include/rt_b200.h declares (tests/test_abi.py checks the list against the header)
 ABI_SYMBOLS = [
-    "rt_init", "rt_shutdown", "rt_last_error", "rt_version",
+    "rt_init", "rt_init_devices", "rt_shutdown", "rt_last_error", "rt_version",
+    "rt_host_frame_alloc", "rt_host_frame_open", "rt_host_frame_free", "rt_render_multi",
     "rt_compile_json_text", "rt_compile_json_file", "rt_compiled_desc", "rt_compiled_free", "rt_compiled_add_dir_light",
     "rt_scene_upload", "rt_scene_free", "rt_scene_size",
     "rt_render", "rt_render_device", "rt_render_paper_device_noalloc", "rt_trace_rays", "rt_debug_jitter", "rt_debug_mt_block_host", "rt_debug_mt_jump_host", "rt_debug_device_layout", "rt_debug_mask_table", "rt_debug_set_option",
@@ -140,6 +141,11 @@ def lib():
         L.rt_measure_fp32_peak.argtypes = [C.POINTER(C.c_double)]
         L.rt_debug_device_layout.argtypes = [C.POINTER(RtSceneDesc), C.c_void_p, C.POINTER(C.c_int), C.c_void_p, C.POINTER(C.c_int), C.c_void_p]
         L.rt_write_png_rgb8.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_int]
+        L.rt_init_devices.argtypes = [C.c_void_p, C.c_int]
+        L.rt_host_frame_alloc.argtypes = [C.c_size_t, C.c_char_p, C.POINTER(C.c_void_p)]
+        L.rt_host_frame_open.argtypes = [C.c_char_p, C.c_size_t, C.POINTER(C.c_void_p)]
+        L.rt_host_frame_free.argtypes = [C.c_void_p]
+        L.rt_render_multi.argtypes = [C.POINTER(RtSceneDesc), C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.POINTER(RtStats)]
         L.rt_peer_frame_create.argtypes = [C.c_size_t, C.POINTER(C.c_void_p), C.c_char_p]
         L.rt_peer_frame_open.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
         L.rt_peer_frame_close.argtypes = [C.c_void_p, C.c_int]
@@ -328,6 +334,46 @@ def measure_fp32_peak() -> float:
     v = C.c_double()
     _check(lib().rt_measure_fp32_peak(C.byref(v)))
     return float(v.value)
+
+
+class HostFrame:
+    """Pinned host memory mapped into the device's address space (rt_host_frame_*): rt_render / rt_render_multi store the
+    packed RGB8 pixels straight into it.  `name` (e.g. "/rt_frame_1234"): backed by POSIX shared memory, so that the ranks
+    of a multi-process job fill ONE frame (rank 0 creates, the others pass create=False)."""
+
+    def __init__(self, height: int, width: int, name: str | None = None, create: bool = True):
+        self.shape = (height, width, 3)
+        self.nbytes = height * width * 3
+        ptr = C.c_void_p()
+        if create:
+            _check(lib().rt_host_frame_alloc(self.nbytes, name.encode() if name else None, C.byref(ptr)))
+        else:
+            _check(lib().rt_host_frame_open(name.encode(), self.nbytes, C.byref(ptr)))
+        self.ptr = int(ptr.value)
+        self.array = np.ctypeslib.as_array((C.c_uint8 * self.nbytes).from_address(self.ptr)).reshape(self.shape)
+
+    def close(self) -> None:
+        if getattr(self, "ptr", 0):
+            self.array = None
+            _check(lib().rt_host_frame_free(C.c_void_p(self.ptr)))
+            self.ptr = 0
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def render_multi(scene: "Scene", mode: "RenderMode", devices, out=None):
+    """Tracer::render on several GPUs from this one process (rt_render_multi).  devices: a count or a list of ordinals;
+    out: a HostFrame (zero-copy) or None (a numpy array is returned).  Returns (rgb8[H,W,3], stats dict)."""
+    devs = list(range(devices)) if isinstance(devices, int) else list(devices)
+    arr = (C.c_int * len(devs))(*devs)
+    st = RtStats()
+    target = out.array if out is not None else np.zeros((scene.height, scene.width, 3), np.uint8)
+    _check(lib().rt_render_multi(C.byref(scene.desc), int(mode), arr, len(devs), target.ctypes.data_as(C.c_void_p), C.byref(st)))
+    return target, st.as_dict()
 
 
 IPC_HANDLE_BYTES = 64

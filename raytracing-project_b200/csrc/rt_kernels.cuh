@@ -19,8 +19,9 @@ namespace rtd {
 // states[b] (one barrier per twist, parallel inside a twist) and leaves the state it ends on in states[b].  With one CTA
 // this is the plain sequential walk from a resume state; with one CTA per segment the segments' start states come from
 // mt_jump_kernel, and the table of a 3840x2160 frame takes ~1 ms instead of 108 ms.
+// Only the tiles a rank owns are kept (tile % world == rank, at local index tile / world): 1/world of the table per GPU.
 __global__ void __launch_bounds__(640) mt_checkpoint_kernel(uint32_t* table, uint32_t* states, long long first_tile, long long n_tiles,
-                                                            long long tiles_per_cta) {
+                                                            long long tiles_per_cta, int rank, int world) {
     __shared__ uint32_t st[2][mt::kN];
     const int k = threadIdx.x;
     const long long t0 = (long long)blockIdx.x * tiles_per_cta;
@@ -31,7 +32,8 @@ __global__ void __launch_bounds__(640) mt_checkpoint_kernel(uint32_t* table, uin
     __syncthreads();
     int cur = 0;
     for (long long j = 0; j < count; ++j) {
-        if (k < mt::kN) table[(first_tile + t0 + j) * mt::kN + k] = st[cur][k];
+        const long long g = first_tile + t0 + j;
+        if (k < mt::kN && g % world == rank) table[(g / world) * mt::kN + k] = st[cur][k];
         for (int b = 0; b < mt::kTwistsPerTile; ++b) {
             if (k < mt::kN) st[cur ^ 1][k] = mt::next_word(st[cur], k);
             __syncthreads();
@@ -92,8 +94,10 @@ __global__ void __launch_bounds__(256) jitter_debug_kernel(const uint32_t* table
 
 // ---------------------------------------------------------------------------------------------------
 struct RenderParams {
-    const uint32_t* mt_table;     // checkpoint per tile (standard mode)
-    uchar4* rgba8;                // H*W, row 0 = top
+    const uint32_t* mt_table;     // checkpoint per LOCAL tile (standard mode): entry k = state at tile rank + k * world
+    uchar4* rgba8;                // optional, H*W, row 0 = top
+    unsigned char* rgb8;          // optional, H*W*3 packed R,G,B, row 0 = top: usually MAPPED HOST memory (the frame leaves the
+                                  // GPU in the kernel's own stores, no copy afterwards); written tile by tile as aligned words
     float4* rgbf;                 // optional
     int* ids;                     // optional, H*W*S
     unsigned long long* counters; // primary, shadow, secondary, tests
@@ -117,6 +121,27 @@ __device__ __forceinline__ void camera_ray(double sx, double sy, V3& o, V3& d) {
     if (L > 1e-6) { const double inv = 1.0 / L; dx *= inv; dy *= inv; dz *= inv; } else { dx = 0; dy = 1; dz = 0; }
     o = mk((float)c_hdr.eye[0], (float)c_hdr.eye[1], (float)c_hdr.eye[2]);
     d = mk((float)dx, (float)dy, (float)dz);
+}
+
+// Host-direct RGB8: the pixels [pix0, pix0 + n_px) of the loop order (standard mode: y from the BOTTOM row, flipped on store,
+// tracer.cpp:297; paper mode: no flip) were staged as packed bytes in shared memory (`s_rgb`, 4-byte aligned) and leave as
+// aligned 32-bit words wherever four staged bytes land on four consecutive, aligned frame bytes (always, when nx % 4 == 0),
+// so that a warp's stores form whole 128-byte PCIe writes; stragglers go byte by byte.  All threads of the CTA call it
+// after a barrier that follows the staging.
+__device__ __forceinline__ long long rgb8_dest(long long p, int c, int nx, int ny, bool flip) {
+    const long long y = p / nx, x = p - y * nx;
+    return 3 * ((flip ? (long long)(ny - 1) - y : y) * nx + x) + c;
+}
+__device__ __forceinline__ void rgb8_flush(unsigned char* __restrict__ dst, const unsigned char* s_rgb, long long pix0, int n_px, int nx, int ny, bool flip) {
+    const int n_bytes = 3 * n_px;
+    for (int b0 = 4 * (int)threadIdx.x; b0 < n_bytes; b0 += 4 * (int)blockDim.x) {
+        const long long d0 = rgb8_dest(pix0 + b0 / 3, b0 % 3, nx, ny, flip);
+        if (b0 + 3 < n_bytes && (d0 & 3) == 0 && rgb8_dest(pix0 + (b0 + 3) / 3, (b0 + 3) % 3, nx, ny, flip) == d0 + 3) {
+            *reinterpret_cast<uint32_t*>(dst + d0) = *reinterpret_cast<const uint32_t*>(s_rgb + b0);
+        } else {
+            for (int b = b0; b < min(b0 + 4, n_bytes); ++b) dst[rgb8_dest(pix0 + b / 3, b % 3, nx, ny, flip)] = s_rgb[b];
+        }
+    }
 }
 
 __device__ __forceinline__ void flush_counters(const Counters& c, unsigned long long* g) {
@@ -155,6 +180,7 @@ template <bool C, bool K, bool F, bool M>
 __global__ void __launch_bounds__(kRenderThreads, RT_MIN_BLOCKS) render_standard_kernel(RenderParams prm) {
     // raw generator words: [0, kN) the tile's checkpoint, then the 8 blocks it yields (tempered on use)
     __shared__ __align__(16) uint32_t raw[mt::kN + mt::kOutputsPerTile];
+    __shared__ __align__(16) unsigned char s_rgb[3 * mt::kPixelsPerTile];      // the tile's packed RGB8 (host-direct output)
     __shared__ int s_tile, s_next;
     const int tid = threadIdx.x;
     constexpr int kWarpGroups = (mt::kSamplesPerTile + 31) / 32;           // 39 groups of 4 pixels per tile
@@ -170,7 +196,7 @@ __global__ void __launch_bounds__(kRenderThreads, RT_MIN_BLOCKS) render_standard
         if (local >= prm.n_local_tiles) break;
         const long long tile = (long long)prm.rank + (long long)local * prm.world;
         // --- the tile's 4992 raw outputs: checkpoint + 8 twists (one barrier each) ---
-        for (int k = tid; k < mt::kN; k += kRenderThreads) raw[k] = __ldg(prm.mt_table + tile * mt::kN + k);
+        for (int k = tid; k < mt::kN; k += kRenderThreads) raw[k] = __ldg(prm.mt_table + (long long)local * mt::kN + k);
         __syncthreads();
 #pragma unroll 1
         for (int b = 0; b < mt::kTwistsPerTile; ++b) {
@@ -224,11 +250,15 @@ __global__ void __launch_bounds__(kRenderThreads, RT_MIN_BLOCKS) render_standard
             if (active && (j & 7) == 0) {
                 c.r *= 0.125f; c.g *= 0.125f; c.b *= 0.125f;              // acc * (1/spp) (tracer.cpp:296)
                 const long long q = (long long)yy * nx + x;
-                prm.rgba8[q] = make_uchar4(to_byte(c.r), to_byte(c.g), to_byte(c.b), 255);
+                const unsigned char r8 = to_byte(c.r), g8 = to_byte(c.g), b8 = to_byte(c.b);
+                if (prm.rgba8) prm.rgba8[q] = make_uchar4(r8, g8, b8, 255);
                 if (prm.rgbf) prm.rgbf[q] = make_float4(c.r, c.g, c.b, 1.f);
+                if (prm.rgb8) { unsigned char* sp = s_rgb + 3 * (j >> 3); sp[0] = r8; sp[1] = g8; sp[2] = b8; }
             }
         }
-        __syncthreads();           // raw / s_tile reuse
+        __syncthreads();           // raw / s_tile reuse; the tile's bytes are staged
+        // (the next tile's first pixel is staged behind two more barriers, after every thread has left this flush)
+        if (prm.rgb8) rgb8_flush(prm.rgb8, s_rgb, pix0, (int)min((long long)mt::kPixelsPerTile, prm.n_pixels - pix0), nx, ny, true);
     }
     flush_counters(cnt, prm.counters);
 }
@@ -290,7 +320,7 @@ __global__ void __launch_bounds__(kRenderThreads, RT_WAVE_BLOCKS) render_wavefro
             if (local >= prm.n_local_tiles) break;
             const long long tile = (long long)prm.rank + (long long)local * prm.world;
             // the tile's 4992 raw outputs: checkpoint + 8 twists (one barrier each)
-            for (int k = tid; k < mt::kN; k += kRenderThreads) st[0][k] = __ldg(prm.mt_table + tile * mt::kN + k);
+            for (int k = tid; k < mt::kN; k += kRenderThreads) st[0][k] = __ldg(prm.mt_table + (long long)local * mt::kN + k);
             __syncthreads();
             int cur = 0;
 #pragma unroll 1
@@ -426,8 +456,15 @@ __global__ void __launch_bounds__(kRenderThreads, RT_WAVE_BLOCKS) render_wavefro
                 const unsigned pg = (unsigned)(pix0 + p);
                 const unsigned y = pg / (unsigned)nx, x = pg - y * (unsigned)nx;
                 const long long qq = (long long)((unsigned)(ny - 1) - y) * nx + x;
-                prm.rgba8[qq] = make_uchar4(to_byte(r), to_byte(g), to_byte(b), 255);
+                const unsigned char r8 = to_byte(r), g8 = to_byte(g), b8 = to_byte(b);
+                if (prm.rgba8) prm.rgba8[qq] = make_uchar4(r8, g8, b8, 255);
                 if (prm.rgbf) prm.rgbf[qq] = make_float4(r, g, b, 1.f);
+                if (prm.rgb8) { unsigned char* s3 = reinterpret_cast<unsigned char*>(outw) + 3 * p; s3[0] = r8; s3[1] = g8; s3[2] = b8; }
+            }
+            if (prm.rgb8) {        // host-direct output: the tile's bytes were staged in `outw` (free since the camera rays were built)
+                __syncthreads();
+                rgb8_flush(prm.rgb8, reinterpret_cast<const unsigned char*>(outw), pix0, n_px, nx, ny, true);
+                __syncthreads();
             }
         }
         __syncthreads();           // s_tile / state reuse
@@ -499,11 +536,16 @@ __device__ __forceinline__ float crosshatch(float L, int x, int y) {
     return line ? 0.f : 1.f;
 }
 
-__global__ void __launch_bounds__(256) paper_post_kernel(const GBuf* __restrict__ gb, uchar4* rgba8, float4* rgbf, int nx, int ny, int rank, int world) {
-    const long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (q >= (long long)nx * ny) return;
-    const int y = (int)(q / nx), x = (int)(q - (long long)y * nx);
-    if (!paper_row_owned(y, rank, world)) return;
+__global__ void __launch_bounds__(256) paper_post_kernel(const GBuf* __restrict__ gb, uchar4* rgba8, float4* rgbf, unsigned char* rgb8,
+                                                         int nx, int ny, int rank, int world) {
+    __shared__ __align__(16) unsigned char s_rgb[3 * 256];               // host-direct output: the block's packed RGB8
+    __shared__ int s_any;
+    const long long q0 = (long long)blockIdx.x * blockDim.x, q = q0 + threadIdx.x;
+    const long long npx = (long long)nx * ny;
+    const int y = q < npx ? (int)(q / nx) : 0, x = q < npx ? (int)(q - (long long)y * nx) : 0;
+    const bool own = q < npx && paper_row_owned(y, rank, world);
+    if (rgb8) { if (threadIdx.x == 0) s_any = 0; __syncthreads(); }
+    if (own) {
     const GBuf c = gb[q];
     // get_edge_strength (tracer.cpp:133-178)
     const int dx[4] = {-1, 1, 0, 0}, dy[4] = {0, 0, -1, 1};
@@ -532,8 +574,26 @@ __global__ void __launch_bounds__(256) paper_post_kernel(const GBuf* __restrict_
         if (edge > 0.3f) v *= (1.f - (edge - 0.3f) * 0.4f);
     }
     const unsigned char b = to_byte(v);
-    rgba8[q] = make_uchar4(b, b, b, 255);                                  // no row flip in paper mode (tracer.cpp:279)
+    if (rgba8) rgba8[q] = make_uchar4(b, b, b, 255);                       // no row flip in paper mode (tracer.cpp:279)
     if (rgbf) rgbf[q] = make_float4(v, v, v, 1.f);
+    if (rgb8) { unsigned char* sp = s_rgb + 3 * threadIdx.x; sp[0] = b; sp[1] = b; sp[2] = b; s_any = 1; }
+    }
+    if (!rgb8) return;
+    __syncthreads();
+    if (!s_any) return;
+    // The block's 256 pixels are consecutive in the frame (no flip): aligned words where all four bytes belong to owned
+    // pixels, single bytes at ownership edges (rows of other ranks inside the block are left untouched).
+    const int n_bytes = 3 * (int)min((long long)256, npx - q0);
+    for (int b0 = 4 * (int)threadIdx.x; b0 < n_bytes; b0 += 4 * (int)blockDim.x) {
+        const long long pa = q0 + b0 / 3, pb = q0 + min(b0 + 3, n_bytes - 1) / 3;
+        const bool oa = paper_row_owned((int)(pa / nx), rank, world), ob = paper_row_owned((int)(pb / nx), rank, world);
+        if (b0 + 3 < n_bytes && oa && ob) {                                    // (four bytes span at most two pixels)
+            *reinterpret_cast<uint32_t*>(rgb8 + 3 * q0 + b0) = *reinterpret_cast<const uint32_t*>(s_rgb + b0);      // 3 * q0 = 768 * block: aligned
+        } else {
+            for (int bb = b0; bb < min(b0 + 4, n_bytes); ++bb)
+                if (paper_row_owned((int)((q0 + bb / 3) / nx), rank, world)) rgb8[3 * q0 + bb] = s_rgb[bb];
+        }
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------
