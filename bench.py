@@ -407,7 +407,8 @@ def run_ours(args) -> None:
     # ---- N > 1: the peer-assembled frame must equal the frame one GPU renders alone, byte for byte (untimed) ----
     frame_equal = None
     if world > 1:
-        assembled = step().clone()
+        assembled = step()
+        assembled = assembled.clone() if assembled is not None else None
         torch.cuda.synchronize()
         if rank == 0:
             alone = torch.zeros((H, W, 4), dtype=torch.uint8, device=dev)
