@@ -447,7 +447,8 @@ int upload_scene(Context& cx, const rt_scene_desc* d, rt_scene** out) {
     h.masks = (const float4*)(base + o_masks); h.mask_scale = s->mask_scale;
     s->width = d->width; s->height = d->height;
     h.n_leaves = d->n_leaves; h.n_ops = d->n_ops;
-    h.off_leaf_geom = s->clustered ? 0 : d->n_objects;               // scenes with clustered runs read top-level geometry from global memory
+    h.off_obj_meta = s->clustered ? 0 : d->n_objects;                // scenes with clustered runs read top-level geometry / meta from global memory
+    h.off_leaf_geom = 2 * h.off_obj_meta;
     h.off_leaf_meta = h.off_leaf_geom + d->n_leaves; h.off_runs = h.off_leaf_meta + d->n_leaves;
     h.off_lights = h.off_runs + (int)s->runs.size();
     h.off_clusters = h.off_lights + 2 * h.n_lights;
@@ -473,11 +474,11 @@ int upload_scene(Context& cx, const rt_scene_desc* d, rt_scene** out) {
     constexpr int kMaxCullWords = 8, kMinCullEntries = 10;
     bool cull = s->cull_words > 0 && s->cull_words <= kMaxCullWords && !s->clustered && !s->bounces && d->n_objects + d->n_leaves >= kMinCullEntries;
     if (opts.cull == 0) cull = false;
-    if (opts.cull == 1) cull = s->cull_words > 0 && s->cull_words <= 96 && !s->clustered;        // test hook: masks wherever they can be built
+    if (opts.cull == 1) cull = s->cull_words > 0 && s->cull_words <= rtd::kCandWordsMax && !s->clustered;        // test hook: masks wherever they can be built
     h.cull_geom = (const float4*)(base + o_cull_geom); h.cull_words = cull ? s->cull_words : 0;
     h.cull_plane_bits = (const uint32_t*)(base + o_cull_plane_bits); h.cull_leaf_word = s->cull_leaf_word;
     h.off_cand_bytes = s->fits_const ? ((h.smem_bytes + 15) & ~15) : 0;
-    s->smem_bytes = (size_t)h.off_cand_bytes + (cull ? sizeof(rtd::CandShared) + (size_t)(1 + rtd::kMaxListLights) * s->cull_words * 4 : 0);
+    s->smem_bytes = (size_t)h.off_cand_bytes + ((cull && !RT_CAND_STATIC) ? sizeof(rtd::CandShared) + (size_t)(1 + rtd::kMaxListLights) * s->cull_words * 4 : 0);
     *out = s;
     return RT_OK;
 }

@@ -25,7 +25,7 @@ struct SceneHeader {
     float bg[3]; float medium_index;
     int recursion, n_objects, n_lights, n_runs, n_leaves, n_ops, n_clusters;
     // shared-memory image (units of 16 B from the start of dynamic shared memory; ops in bytes)
-    int off_leaf_geom, off_leaf_meta, off_runs, off_lights, off_clusters, off_masks, off_ops_bytes, smem_bytes;
+    int off_obj_meta, off_leaf_geom, off_leaf_meta, off_runs, off_lights, off_clusters, off_masks, off_ops_bytes, smem_bytes;
     float mask_scale;           // unused by the device since the margin moved into the table (kept for rt_debug_mask_table)
     const float4* obj_geom; const int4* obj_meta;
     const float4* leaf_geom; const int4* leaf_meta;
@@ -69,7 +69,13 @@ template <bool C> struct SV {
     // Scenes with bounds (K) do not stage the top-level geometry: the scan reads the mask table, geometry is only needed to
     // finish the few candidates, and without it the 1 100-primitive scene keeps 4 CTAs per SM (43 -> 26 KB per CTA).
     template <bool K> static __device__ __forceinline__ float4 obj_geom_k(int i) { return (C && !K) ? reinterpret_cast<const float4*>(s_scene)[i] : __ldg(c_hdr.obj_geom + i); }
-    static __device__ __forceinline__ int4   obj_meta(int i)  { return __ldg(c_hdr.obj_meta + i); }
+    // object meta: staged next to the geometry (scenes without bounds: the masked scans read it per candidate), else global
+#ifndef RT_META_SMEM
+#define RT_META_SMEM 1
+#endif
+    template <bool K> static __device__ __forceinline__ int4 obj_meta_k(int i) {
+        return (RT_META_SMEM && C && !K) ? reinterpret_cast<const int4*>(s_scene)[c_hdr.off_obj_meta + i] : __ldg(c_hdr.obj_meta + i);
+    }
     static __device__ __forceinline__ float4 leaf_geom(int i) { return C ? reinterpret_cast<const float4*>(s_scene)[c_hdr.off_leaf_geom + i] : __ldg(c_hdr.leaf_geom + i); }
     static __device__ __forceinline__ int4   leaf_meta(int i) { return C ? reinterpret_cast<const int4*>(s_scene)[c_hdr.off_leaf_meta + i] : __ldg(c_hdr.leaf_meta + i); }
     static __device__ __forceinline__ float4 pokeball(int i, int k) { return __ldg(c_hdr.pokeballs + i * 3 + k); }
@@ -97,7 +103,10 @@ template <bool C> __device__ __forceinline__ void stage_scene() {
     if (!C) return;
     float4* dst = reinterpret_cast<float4*>(s_scene);
     const int t = threadIdx.x, n = blockDim.x;
-    for (int i = t; i < c_hdr.off_leaf_geom; i += n) dst[i] = __ldg(c_hdr.obj_geom + i);      // 0 entries when the scene has bounds
+    for (int i = t; i < c_hdr.off_obj_meta; i += n) {                                         // 0 entries when the scene has bounds
+        dst[i] = __ldg(c_hdr.obj_geom + i);
+        reinterpret_cast<int4*>(dst)[c_hdr.off_obj_meta + i] = __ldg(c_hdr.obj_meta + i);
+    }
     for (int i = t; i < c_hdr.n_leaves; i += n) {
         dst[c_hdr.off_leaf_geom + i] = __ldg(c_hdr.leaf_geom + i);
         reinterpret_cast<int4*>(dst)[c_hdr.off_leaf_meta + i] = __ldg(c_hdr.leaf_meta + i);
@@ -170,10 +179,24 @@ struct CandShared {
     int pad[2];
     // followed by (1 + kMaxListLights) * c_hdr.cull_words mask words
 };
+// The boxes and the mask words live in STATIC shared memory: their addresses are compile-time constants (behind the staged
+// scene they cost a constant-bank load and an add at every use: 2.6 % of the snorlax kernel's instructions).
+constexpr int kCandWordsMax = 16;          // words per bundle: scenes of up to 512 cullable entries (the library picks <= 8)
+#ifndef RT_CAND_STATIC
+#define RT_CAND_STATIC 1
+#endif
+#if RT_CAND_STATIC
+__device__ __forceinline__ CandShared* cand_shared() { __shared__ CandShared S; return &S; }
+__device__ __forceinline__ uint32_t* cand_words(int bundle) {
+    __shared__ uint32_t words[(1 + kMaxListLights) * kCandWordsMax];
+    return words + bundle * kCandWordsMax;
+}
+#else
 __device__ __forceinline__ CandShared* cand_shared() { return reinterpret_cast<CandShared*>(s_scene + c_hdr.off_cand_bytes); }
 __device__ __forceinline__ uint32_t* cand_words(int bundle) {
     return reinterpret_cast<uint32_t*>(s_scene + c_hdr.off_cand_bytes + sizeof(CandShared)) + bundle * c_hdr.cull_words;
 }
+#endif
 __device__ __forceinline__ int f2ord(float f) { const int i = __float_as_int(f); return i ^ ((i >> 31) & 0x7fffffff); }
 __device__ __forceinline__ float ord2f(int i) { return __int_as_float(i ^ ((i >> 31) & 0x7fffffff)); }
 constexpr int kOrdPosInf = 0x7f800000, kOrdNegInf = (int)0x807fffff;      // f2ord(+inf), f2ord(-inf)
@@ -215,29 +238,40 @@ __device__ __forceinline__ void cand_build(int b0, int nb, unsigned& tests) {
     for (int k = 0; k < 3; ++k) { lo[k] = ord2f(b0 == 0 ? S->dir_lo[k] : S->org_lo[k]); hi[k] = ord2f(b0 == 0 ? S->dir_hi[k] : S->org_hi[k]); }
     const bool empty = !(lo[0] <= hi[0]);                         // no ray contributed: nothing will be asked
     const float eps_max = __int_as_float(S->eps_max);
-    int cur = -1; Bundle B; B.wide = 1; B.t_hi = 0.f; B.h = 0.f; B.kd = 0.f; B.inv1md = 1.f; B.mx = B.my = B.mz = 0.f; B.cx = B.cy = B.cz = 0.f;
+    Bundle B; B.wide = 1; B.t_hi = 0.f; B.h = 0.f; B.kd = 0.f; B.inv1md = 1.f; B.mx = B.my = B.mz = 0.f; B.cx = B.cy = B.cz = 0.f;
     if (!empty && !nan) {
-        for (int k = threadIdx.x >> 5; k < nb * W; k += nwarps) {   // (empty and no NaN: no ray will ask)
-            const int bb = k / W, w = k - bb * W, b = b0 + bb;
-            if (bb != cur) {
-                cur = bb;
-                if (b == 0) { const float eye[3] = {(float)c_hdr.eye[0], (float)c_hdr.eye[1], (float)c_hdr.eye[2]}; bundle_from_dirbox(B, eye, lo, hi); }
-                else {
-                    const float4 lp = __ldg(c_hdr.lights + 2 * (b - 1));
-                    const float L[3] = {lp.x, lp.y, lp.z};
-                    bundle_from_box_light(B, lo, hi, eps_max, L, lp.w != 0.f);
-                }
+        // A task = one bundle x `chunk` consecutive words: the bundle is set up once per task, and the tasks are sized so that
+        // they spread evenly over the warps (snorlax: 5 lights x 2 words -> 5 tasks of 2 words instead of 10 tasks on 8 warps).
+#ifndef RT_CAND_CHUNK
+#define RT_CAND_CHUNK 0          // measured: snorlax 4K 10.50 (off) vs 10.72 ms (on)
+#endif
+        const int chunk = RT_CAND_CHUNK ? max(1, min(W, (nb * W + nwarps - 1) / nwarps)) : 1;
+        const int per_bundle = (W + chunk - 1) / chunk;
+        int bb = 0, part = threadIdx.x >> 5;                       // task k = bb * per_bundle + part
+        while (part >= per_bundle) { part -= per_bundle; ++bb; }
+        while (bb < nb) {                                          // (empty and no NaN: no ray will ask)
+            const int b = b0 + bb;
+            if (b == 0) { const float eye[3] = {(float)c_hdr.eye[0], (float)c_hdr.eye[1], (float)c_hdr.eye[2]}; bundle_from_dirbox(B, eye, lo, hi); }
+            else {
+                const float4 lp = __ldg(c_hdr.lights + 2 * (b - 1));
+                const float L[3] = {lp.x, lp.y, lp.z};
+                bundle_from_box_light(B, lo, hi, eps_max, L, lp.w != 0.f);
             }
-            const float4 g = __ldg(c_hdr.cull_geom + 32 * w + lane);
-            const bool plane = (__ldg(c_hdr.cull_plane_bits + w) >> lane) & 1u;
-            Sphere4 q; q.x = g.x; q.y = g.y; q.z = g.z; q.w = g.w;
-            // padding entries have w < 0; CSG leaves (words from cull_leaf_word on) are culled on the whole line
-            // (a bundle too wide to cull — a round across a silhouette, a light inside the box — keeps every entry)
-            // (a plane's w is its offset n.p0 and may well be negative: only non-plane entries use w < 0 as "padding")
-            const bool cand = plane ? (B.wide || !bundle_rejects_plane(B, q)) : (g.w >= 0.f && (B.wide || !bundle_rejects(B, q, B.t_hi, w < c_hdr.cull_leaf_word)));
-            ++tests;
-            const uint32_t bits = __ballot_sync(kFullWarp, cand);
-            if (lane == 0) cand_words(b)[w] = bits;
+            const int w_end = min(W, (part + 1) * chunk);
+            for (int w = part * chunk; w < w_end; ++w) {
+                const float4 g = __ldg(c_hdr.cull_geom + 32 * w + lane);
+                const bool plane = (__ldg(c_hdr.cull_plane_bits + w) >> lane) & 1u;
+                Sphere4 q; q.x = g.x; q.y = g.y; q.z = g.z; q.w = g.w;
+                // padding entries have w < 0; CSG leaves (words from cull_leaf_word on) are culled on the whole line
+                // (a bundle too wide to cull — a round across a silhouette, a light inside the box — keeps every entry)
+                // (a plane's w is its offset n.p0 and may well be negative: only non-plane entries use w < 0 as "padding")
+                const bool cand = plane ? (B.wide || !bundle_rejects_plane(B, q)) : (g.w >= 0.f && (B.wide || !bundle_rejects(B, q, B.t_hi, w < c_hdr.cull_leaf_word)));
+                ++tests;
+                const uint32_t bits = __ballot_sync(kFullWarp, cand);
+                if (lane == 0) cand_words(b)[w] = bits;
+            }
+            part += nwarps;
+            while (part >= per_bundle) { part -= per_bundle; ++bb; }
         }
     } else if (nan) {                                             // a NaN among the rays: keep every entry
         for (int k = threadIdx.x >> 5; k < nb * W; k += nwarps) {

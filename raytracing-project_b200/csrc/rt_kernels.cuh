@@ -93,6 +93,10 @@ __global__ void __launch_bounds__(256) jitter_debug_kernel(const uint32_t* table
 }
 
 // ---------------------------------------------------------------------------------------------------
+// A/B build switch: 1 = no host-direct output code in the kernels
+#ifndef RT_NO_DIRECT
+#define RT_NO_DIRECT 0
+#endif
 struct RenderParams {
     const uint32_t* mt_table;     // checkpoint per LOCAL tile (standard mode): entry k = state at tile rank + k * world
     uchar4* rgba8;                // optional, H*W, row 0 = top
@@ -167,6 +171,39 @@ __device__ __forceinline__ const uint32_t* camera_mask(bool active, V3 d, Counte
     return cand_of(0);
 }
 
+// The camera mask of a whole TILE (render_standard_kernel): instead of reducing the directions of every round's rays (two
+// barriers and a mask build per 32 pixels), ONE thread bounds the directions of all camera rays of the tile's pixels
+// [pix0, pix0 + n_px) analytically and the CTA builds the camera mask once per tile.  A sample of pixel (x, y) passes through
+// the screen point P + (lx (x + u) / nx, ly (y + v) / ny, 0) with u, v in [0, 1) (camera.h:68-78, tracer.cpp:290-293), so with
+// D = that point - eye inside the box [ax, bx] x [ay, by] x {c} and |D| inside [Lmin, Lmax] every component of D / |D| lies
+// between its quotients by the two lengths.  The box is inflated far beyond the rounding of the rays' own FP64 -> FP32
+// arithmetic; tiles that straddle a row take the whole row (their bundle comes out wide: every entry stays a candidate).
+#ifndef RT_TILE_CAMERA_MASK
+#define RT_TILE_CAMERA_MASK 1
+#endif
+__device__ __forceinline__ void tile_direction_box(long long pix0, int n_px, int nx, int ny) {
+    CandShared* S = cand_shared();
+    const long long y0 = pix0 / nx, y1 = (pix0 + n_px - 1) / nx;
+    const double x_lo = y0 == y1 ? (double)(pix0 - y0 * nx) : 0.0, x_hi = y0 == y1 ? (double)(pix0 + n_px - y0 * nx) : (double)nx;
+    double a[3], b[3];
+    { const double u = c_hdr.P[0] + c_hdr.lx * (x_lo / nx) - c_hdr.eye[0], v = c_hdr.P[0] + c_hdr.lx * (x_hi / nx) - c_hdr.eye[0]; a[0] = fmin(u, v); b[0] = fmax(u, v); }
+    { const double u = c_hdr.P[1] + c_hdr.ly * ((double)y0 / ny) - c_hdr.eye[1], v = c_hdr.P[1] + c_hdr.ly * ((double)(y1 + 1) / ny) - c_hdr.eye[1]; a[1] = fmin(u, v); b[1] = fmax(u, v); }
+    a[2] = b[2] = c_hdr.P[2] - c_hdr.eye[2];
+    double l2min = 0.0, l2max = 0.0;
+    for (int k = 0; k < 3; ++k) {
+        const double m = (a[k] <= 0.0 && b[k] >= 0.0) ? 0.0 : fmin(a[k] * a[k], b[k] * b[k]);
+        l2min += m; l2max += fmax(a[k] * a[k], b[k] * b[k]);
+    }
+    const bool degenerate = !(l2min > 1e-9) || !(l2max < 1e300);          // (camera.h:72-76: L <= 1e-6 falls back to +Y; NaN)
+    const double inv_min = 1.0 / sqrt(l2min), inv_max = 1.0 / sqrt(l2max); // 1 / Lmin >= 1 / Lmax
+    for (int k = 0; k < 3; ++k) {
+        double lo = a[k] >= 0.0 ? a[k] * inv_max : a[k] * inv_min, hi = b[k] >= 0.0 ? b[k] * inv_min : b[k] * inv_max;
+        if (degenerate) { lo = -1.0; hi = 1.0; }
+        S->dir_lo[k] = f2ord((float)lo - 2e-6f);                           // (the rays' directions are rounded to float: 6e-8)
+        S->dir_hi[k] = f2ord((float)hi + 2e-6f);
+    }
+}
+
 // 4 CTAs x 256 threads per SM = 64 registers per thread: occupancy (32 warps/SM) is worth more here than registers;
 // measured against 2 (128 regs) and 3 (80 regs) on four scenes, see profiles/.
 #ifndef RT_MIN_BLOCKS
@@ -197,22 +234,33 @@ __global__ void __launch_bounds__(kRenderThreads, RT_MIN_BLOCKS) render_standard
         const long long tile = (long long)prm.rank + (long long)local * prm.world;
         // --- the tile's 4992 raw outputs: checkpoint + 8 twists (one barrier each) ---
         for (int k = tid; k < mt::kN; k += kRenderThreads) raw[k] = __ldg(prm.mt_table + (long long)local * mt::kN + k);
+        const long long pix0 = tile * mt::kPixelsPerTile;
+        if (M && RT_TILE_CAMERA_MASK && tid == kRenderThreads - 1) tile_direction_box(pix0, (int)min((long long)mt::kPixelsPerTile, prm.n_pixels - pix0), nx, ny);
         __syncthreads();
 #pragma unroll 1
         for (int b = 0; b < mt::kTwistsPerTile; ++b) {
             for (int k = tid; k < mt::kN; k += kRenderThreads) raw[(b + 1) * mt::kN + k] = mt::next_word(raw + b * mt::kN, k);
             __syncthreads();
         }
+        if (M && RT_TILE_CAMERA_MASK) cand_build(0, 1, cnt.tests);         // the tile's camera mask (barrier inside)
         // --- one sample per thread; 8 consecutive lanes share a pixel.  With round-level culling the tile's 39 groups of 32
         // samples are dealt statically, 8 groups = 32 neighbouring pixels per round: the CTA walks a round together (camera
         // mask, camera rays, shadow masks, shadow rays; rt_trace.cuh).  Scenes too large for the masks take groups from a
         // shared counter instead, so a warp that drew expensive samples traces fewer groups. ---
-        const long long pix0 = tile * mt::kPixelsPerTile;
-        constexpr bool lists = M;
+        // Round-level masks: kListsCta (default) = the CTA walks 8 groups per round in step and builds the shadow masks together;
+        // kListsWarp (A/B build switch RT_WARP_MASKS=1) = every warp culls the scene against the shadow bundles of its own 32
+        // samples and takes its groups from the shared counter like the kernels without masks: no barriers, tighter bundles,
+        // but 8x the culling work — it only pays for one-word tables with few lights.
+#ifndef RT_WARP_MASKS
+#define RT_WARP_MASKS 0          // measured (4K): snorlax 11.59 vs 10.51 ms, reflect variant 17.8 vs 13.9, penguin 5.41 vs 5.75
+#endif
+        static_assert(!RT_WARP_MASKS || RT_TILE_CAMERA_MASK, "warp-level shadow masks need the per-tile camera mask");
+        static_assert(kWarps <= kMaxListLights, "one mask slot per warp");
+        constexpr int lists = !M ? kListsNone : RT_WARP_MASKS ? kListsWarp : kListsCta;
 #pragma unroll 1
         for (int round = 0;; ++round) {
             int grp;
-            if (lists) {
+            if (lists == kListsCta) {
                 if (round * kWarps >= kWarpGroups) break;
                 grp = round * kWarps + (tid >> 5);
             } else {
@@ -236,7 +284,7 @@ __global__ void __launch_bounds__(kRenderThreads, RT_MIN_BLOCKS) render_standard
                 camera_ray(sx, sy, o, d);
             }
             {   // with masks all threads of the CTA make these calls (barriers inside); a thread without a sample keeps company
-                const uint32_t* cand0 = lists ? camera_mask(active, d, cnt) : nullptr;
+                const uint32_t* cand0 = lists == kListsNone ? nullptr : RT_TILE_CAMERA_MASK ? cand_of(0) : camera_mask(active, d, cnt);
                 Hit ph; bool phit;
                 c = trace<C, K, M, F, RT_MAX_RECURSION>(active, lists, cand0, o, d, ph, phit, cnt);
                 if (active && prm.ids) prm.ids[((long long)yy * nx + x) * 8 + (j & 7)] = phit ? ph.code : -1;
@@ -253,12 +301,12 @@ __global__ void __launch_bounds__(kRenderThreads, RT_MIN_BLOCKS) render_standard
                 const unsigned char r8 = to_byte(c.r), g8 = to_byte(c.g), b8 = to_byte(c.b);
                 if (prm.rgba8) prm.rgba8[q] = make_uchar4(r8, g8, b8, 255);
                 if (prm.rgbf) prm.rgbf[q] = make_float4(c.r, c.g, c.b, 1.f);
-                if (prm.rgb8) { unsigned char* sp = s_rgb + 3 * (j >> 3); sp[0] = r8; sp[1] = g8; sp[2] = b8; }
+                if (!RT_NO_DIRECT && prm.rgb8) { unsigned char* sp = s_rgb + 3 * (j >> 3); sp[0] = r8; sp[1] = g8; sp[2] = b8; }
             }
         }
         __syncthreads();           // raw / s_tile reuse; the tile's bytes are staged
         // (the next tile's first pixel is staged behind two more barriers, after every thread has left this flush)
-        if (prm.rgb8) rgb8_flush(prm.rgb8, s_rgb, pix0, (int)min((long long)mt::kPixelsPerTile, prm.n_pixels - pix0), nx, ny, true);
+        if (!RT_NO_DIRECT && prm.rgb8) rgb8_flush(prm.rgb8, s_rgb, pix0, (int)min((long long)mt::kPixelsPerTile, prm.n_pixels - pix0), nx, ny, true);
     }
     flush_counters(cnt, prm.counters);
 }
@@ -459,9 +507,9 @@ __global__ void __launch_bounds__(kRenderThreads, RT_WAVE_BLOCKS) render_wavefro
                 const unsigned char r8 = to_byte(r), g8 = to_byte(g), b8 = to_byte(b);
                 if (prm.rgba8) prm.rgba8[qq] = make_uchar4(r8, g8, b8, 255);
                 if (prm.rgbf) prm.rgbf[qq] = make_float4(r, g, b, 1.f);
-                if (prm.rgb8) { unsigned char* s3 = reinterpret_cast<unsigned char*>(outw) + 3 * p; s3[0] = r8; s3[1] = g8; s3[2] = b8; }
+                if (!RT_NO_DIRECT && prm.rgb8) { unsigned char* s3 = reinterpret_cast<unsigned char*>(outw) + 3 * p; s3[0] = r8; s3[1] = g8; s3[2] = b8; }
             }
-            if (prm.rgb8) {        // host-direct output: the tile's bytes were staged in `outw` (free since the camera rays were built)
+            if (!RT_NO_DIRECT && prm.rgb8) {        // host-direct output: the tile's bytes were staged in `outw` (free since the camera rays were built)
                 __syncthreads();
                 rgb8_flush(prm.rgb8, reinterpret_cast<const unsigned char*>(outw), pix0, n_px, nx, ny, true);
                 __syncthreads();

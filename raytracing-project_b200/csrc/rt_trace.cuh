@@ -20,7 +20,7 @@ namespace rtd {
 template <bool C, bool K>
 __device__ __forceinline__ bool generic_hit(int i, V3 o, V3 d, float tmin, float tmax, const uint32_t* leafw, float& t_out,
                                             uint32_t& code_out, float& tent_out, unsigned& tests) {
-    const int4 m = SV<C>::obj_meta(i);
+    const int4 m = SV<C>::template obj_meta_k<K>(i);
     const int kind = m.x & 0xff, flags = m.x >> 8;
     if (flags & RT_FLAG_NEVER) return false;
     const bool wrapped = flags & RT_FLAG_WRAPPED;
@@ -83,7 +83,7 @@ __device__ __forceinline__ void scan_masked(V3 o, V3 d, float tmin, float tmax, 
         uint32_t bits = cand[w];
         while (bits) {
             const int i = (w << 5) + __ffs(bits) - 1; bits &= bits - 1;
-            const int4 m = SV<C>::obj_meta(i);
+            const int4 m = SV<C>::template obj_meta_k<K>(i);
             const int kind = m.x & 0xff;
             float t;
             if ((m.x >> 8) == 0 && kind != RT_PRIM_PROGRAM) {
@@ -212,7 +212,7 @@ __device__ __forceinline__ bool closest_hit(V3 o, V3 d, float tmin, float tmax, 
     const int best = sr.best;
     if (best < 0) return false;
     // ---- finalise the winner: normal, front_face, material, id code ----
-    const int4 m = SV<C>::obj_meta(best);
+    const int4 m = SV<C>::template obj_meta_k<K>(best);
     const int kind = m.x & 0xff, flags = m.x >> 8;
     hit.t = sr.t;
     hit.code = SV<C>::obj_orig(best) * 8;
@@ -303,17 +303,23 @@ __device__ __forceinline__ void light_shade(int l, const float4 m0, float ks, fl
 // shade_lambert_phong for a thread with `lit` (a hit with a material); the others get (0,0,0).  Two passes per chunk of 32
 // lights: all shadow queries first (one visibility bit each), the contributions of the visible lights after, so that no
 // shading state is live across the scans.
-// LISTS (CTA-uniform): the call is made by ALL threads of the CTA for the camera rays of one round; the CTA first reduces the box of the
-// shadow-ray origins and culls the scene against the bundle towards every light (cand_build, two barriers), and the shadow
-// scans take their candidates from those masks.  Without LISTS (secondary rays, known-answer rays) the scans use the
-// per-lane mask only and the call may come from divergent code.
+// LISTS (uniform over the callers): how the shadow scans get their candidates.
+//   kListsNone  per-lane conservative masks only; the call may come from divergent code (secondary rays, known-answer rays);
+//   kListsCta   the call is made by ALL threads of the CTA for the camera rays of one round: the CTA reduces the box of the
+//               shadow-ray origins and culls the scene against the bundle towards every light (cand_build, two barriers);
+//   kListsWarp  the call is made by all 32 lanes of a WARP for its 32 camera rays (4 neighbouring pixels): the warp reduces
+//               the box of its own shadow-ray origins into uniform registers and, light by light, culls the scene against the
+//               bundle towards that light, one entry per lane, into its own mask words — no barrier, no shared atomics, and
+//               the warps of a CTA need not walk in step.
+enum { kListsNone = 0, kListsCta = 1, kListsWarp = 2 };
 template <bool C, bool K, bool M>
-__device__ __forceinline__ RGBf shade(bool lit, const bool LISTS, const Hit& h, V3 p, V3 wo, Counters& cnt) {
+__device__ __forceinline__ RGBf shade(bool lit, const int LISTS, const Hit& h, V3 p, V3 wo, Counters& cnt) {
     const float eps = fmaxf(1e-3f, 1e-4f * h.t);                             // shading.cpp:43
     const V3 so = madd(p, h.n, eps);
     const int nl = c_hdr.n_lights;
-    const bool lists = M && LISTS;
-    if (lists) {
+    const int lists = M ? LISTS : kListsNone;
+    float blo[3] = {0.f, 0.f, 0.f}, bhi[3] = {0.f, 0.f, 0.f}, beps = 0.f; bool bok = false;      // kListsWarp: the warp's origin box
+    if (lists == kListsCta) {
         CandShared* S = cand_shared();
         cand_box_add(lit, so, S->org_lo, S->org_hi, &S->nan_flags, 2);
         const float e = warp_max_nan(lit ? eps : 0.f);
@@ -322,23 +328,57 @@ __device__ __forceinline__ RGBf shade(bool lit, const bool LISTS, const Hit& h, 
         cand_build(1, min(nl, kMaxListLights), cnt.tests);
         if (threadIdx.x < 3) { S->org_lo[threadIdx.x] = kOrdPosInf; S->org_hi[threadIdx.x] = kOrdNegInf; }     // for the next round
         if (threadIdx.x == 3) { S->eps_max = 0; atomicAnd(&S->nan_flags, ~2); }
+    } else if (lists == kListsWarp) {
+        blo[0] = warp_min_nan(lit ? so.x : kInf); blo[1] = warp_min_nan(lit ? so.y : kInf); blo[2] = warp_min_nan(lit ? so.z : kInf);
+        bhi[0] = warp_max_nan(lit ? so.x : -kInf); bhi[1] = warp_max_nan(lit ? so.y : -kInf); bhi[2] = warp_max_nan(lit ? so.z : -kInf);
+        beps = warp_max_nan(lit ? eps : 0.f);
+        // (a NaN anywhere fails these comparisons: the warp then scans without masks)
+        bok = blo[0] <= bhi[0] && blo[1] <= bhi[1] && blo[2] <= bhi[2] && beps >= 0.f;
     }
     RGBf E = rgb(0.f, 0.f, 0.f);
-    if (!lit) return E;
-    { const float4 m1 = material(h.mat, 1); E = rgb(m1.x, m1.y, m1.z); }       // ambient (x) scene ambient, pre-multiplied
+    if (lists != kListsWarp && !lit) return E;
+    if (lit) { const float4 m1 = material(h.mat, 1); E = rgb(m1.x, m1.y, m1.z); }       // ambient (x) scene ambient, pre-multiplied
+    uint32_t* my_words = lists == kListsWarp ? cand_words(1 + (int)(threadIdx.x >> 5)) : nullptr;
     for (int l0 = 0; l0 < nl; l0 += 32) {
         const int cnt_l = min(32, nl - l0);
         uint32_t vis = 0;
         for (int k = 0; k < cnt_l; ++k) {
             V3 wi; float dist;
-            const float ndotl = light_vector(SV<C>::light(l0 + k, 0), p, h.n, wi, dist);
-            if (ndotl <= 0.f) continue;                                      // shading.cpp:51,94
+            const float4 lp = SV<C>::light(l0 + k, 0);
+            const float ndotl = light_vector(lp, p, h.n, wi, dist);
             const float tmaxS = dist - eps;
-            if (tmaxS <= eps) continue;                                      // shading.cpp:98
-            ++cnt.shadow;
-            const uint32_t* cand = lists ? cand_of(1 + l0 + k) : nullptr;
-            if (!occluded<C, K, M>(so, normalized(wi), eps, tmaxS, cand, cnt)) vis |= 1u << k;   // Ray ctor re-normalises (core.h:278)
+            const bool need = lit && !(ndotl <= 0.f) && !(tmaxS <= eps);     // shading.cpp:51,94 / :98
+            const uint32_t* cand = nullptr;
+            if (lists == kListsWarp) {
+                if (!__any_sync(kFullWarp, need)) continue;                 // (warp-uniform)
+                if (bok) {
+                    Bundle B;
+                    const float L[3] = {lp.x, lp.y, lp.z};
+                    bundle_from_box_light(B, blo, bhi, beps, L, lp.w != 0.f);
+                    const int W = c_hdr.cull_words, lane = threadIdx.x & 31;
+                    for (int w = 0; w < W; ++w) {
+                        const float4 g = __ldg(c_hdr.cull_geom + 32 * w + lane);
+                        const bool plane = (__ldg(c_hdr.cull_plane_bits + w) >> lane) & 1u;
+                        Sphere4 q; q.x = g.x; q.y = g.y; q.z = g.z; q.w = g.w;
+                        const bool c1 = plane ? (B.wide || !bundle_rejects_plane(B, q)) : (g.w >= 0.f && (B.wide || !bundle_rejects(B, q, B.t_hi, w < c_hdr.cull_leaf_word)));
+                        ++cnt.tests;
+                        const uint32_t bits = __ballot_sync(kFullWarp, c1);
+                        if (lane == 0) my_words[w] = bits;
+                    }
+                    __syncwarp();
+                    cand = my_words;
+                }
+            } else {
+                if (!need) continue;
+                if (lists == kListsCta) cand = cand_of(1 + l0 + k);
+            }
+            if (need) {
+                ++cnt.shadow;
+                if (!occluded<C, K, M>(so, normalized(wi), eps, tmaxS, cand, cnt)) vis |= 1u << k;   // Ray ctor re-normalises (core.h:278)
+            }
+            if (lists == kListsWarp) __syncwarp();                          // the words are rewritten for the next light
         }
+        if (!lit) continue;
         const float4 m0 = material(h.mat, 0), m2 = material(h.mat, 2);
         while (vis) {
             const int k = __ffs(vis) - 1; vis &= vis - 1;
@@ -361,7 +401,7 @@ __device__ __forceinline__ RGBf shade(bool lit, const bool LISTS, const Hit& h, 
 // recursion == 1): no frames are touched and every tree finishes with its first ray.  LISTS: the ray is a camera ray of
 // a round — `cand` is the round's mask of the camera bundle, ALL threads of the CTA make the call (see shade).
 template <bool C, bool K, bool M, bool FLAT>
-__device__ __forceinline__ bool ray_step(bool alive, const bool LISTS, const uint32_t* cand, V3& o, V3& d, int& sp, float4* __restrict__ frames,
+__device__ __forceinline__ bool ray_step(bool alive, const int LISTS, const uint32_t* cand, V3& o, V3& d, int& sp, float4* __restrict__ frames,
                                          RGBf& result, Hit& primary, bool& primary_hit, Counters& cnt) {
     const int limit = c_hdr.recursion;
     Hit h; h.mat = -1; h.t = 0.f; h.n = mk(0.f, 1.f, 0.f); h.front = true; h.code = -1;
@@ -443,7 +483,7 @@ __device__ __forceinline__ bool ray_step(bool alive, const bool LISTS, const uin
 // available = deepest recursion served.  LISTS: the sample is a camera ray of a round whose camera-bundle mask is `cand`;
 // ALL threads of the CTA make the call (the first ray and its shadow rays use the round's masks, deeper rays none).
 template <bool C, bool K, bool M, bool FLAT, int D>
-__device__ __forceinline__ RGBf trace(bool active, const bool LISTS, const uint32_t* cand, V3 o, V3 d, Hit& primary, bool& primary_hit, Counters& cnt) {
+__device__ __forceinline__ RGBf trace(bool active, const int LISTS, const uint32_t* cand, V3 o, V3 d, Hit& primary, bool& primary_hit, Counters& cnt) {
     primary_hit = false;
     RGBf result = rgb(0.f, 0.f, 0.f);
     if (c_hdr.recursion <= 0) {                                              // tracer.cpp:26 at depth 0: black, ids still defined
@@ -457,11 +497,11 @@ __device__ __forceinline__ RGBf trace(bool active, const bool LISTS, const uint3
     }
     float4 frames[3 * D];
     int sp = 0;                     // == depth of the ray being traced
-    bool lists = LISTS;             // the camera ray: all threads; deeper rays: the threads whose tree goes on, no masks
+    int lists = LISTS;              // the camera ray: all threads; deeper rays: the threads whose tree goes on, no masks
     for (;;) {
         const bool done = ray_step<C, K, M, false>(active, lists, lists ? cand : nullptr, o, d, sp, frames, result, primary, primary_hit, cnt);
         if (!active || done) break;
-        lists = false;
+        lists = kListsNone;
     }
     return result;
 }
