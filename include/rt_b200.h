@@ -223,8 +223,8 @@ int rt_render_device(rt_scene*, int mode, int rank, int world,
  * request of the run's operators.  Same pixels as rt_render_device(scene, RT_MODE_PAPER, rank, world, rgba8_device,
  * NULL, NULL, stream, NULL), but the G-buffer between the two passes lives in a file-scope static __device__ array
  * instead of a grown cudaMalloc buffer, and the call itself performs no cudaMalloc / cudaFree / allocating library call.
- *   - limit: width * height <= RT_NOALLOC_MAX_PIXELS (1280 x 1024; 32 B of G-buffer per pixel + 256 B of counters =
- *     40 MiB of device memory held by every GPU that loads the library, until the process exits); larger frames are
+ *   - limit: width * height <= RT_NOALLOC_MAX_PIXELS (1280 x 1024; 20 B of G-buffer per pixel + 256 B of counters =
+ *     25 MiB of device memory held by every GPU that loads the library, until the process exits); larger frames are
  *     rejected with RT_ERR_LIMIT and a message naming the limit;
  *   - rt_init and rt_scene_upload (which do allocate) must have been called before; rgba8_device is the caller's
  *     H*W uchar4 buffer; stream as in rt_render_device; asynchronous: order your reads after `stream`;

@@ -54,7 +54,7 @@ struct ContextState {
     const void* const_owner{nullptr};     // which scene currently occupies constant memory
     // frame buffers of the host-output path (rt_render): owned by the context and grown on demand, so that a
     // fresh scene (the CLI, the bench's end-to-end leg) does not pay cudaMalloc/cudaFree of ~100 MB per frame
-    uchar4* d_rgba8{nullptr}; float4* d_rgbf{nullptr}; int* d_ids{nullptr}; rtd::GBuf* d_gbuf{nullptr}; unsigned char* d_pack{nullptr};
+    uchar4* d_rgba8{nullptr}; float4* d_rgbf{nullptr}; int* d_ids{nullptr}; unsigned char* d_gbuf{nullptr}; unsigned char* d_pack{nullptr};
     size_t rgba8_cap{0}, rgbf_cap{0}, ids_cap{0}, gbuf_cap{0}, pack_cap{0};     // bytes
     float4* d_wave{nullptr}; size_t wave_cap{0};                                  // wavefront kernel: per-CTA sample state
 };
@@ -576,7 +576,9 @@ template <class T> int grow(T** p, size_t* cap, size_t bytes) {
 }
 
 // paper_gbuffer_kernel variant: <scene staged in shared memory, clustered runs, round-level masks>
-using PaperKernel = void (*)(rtd::GBuf*, int*, unsigned long long*, int, int);
+using PaperKernel = void (*)(rtd::GBuf, int*, unsigned long long*, int, int);
+// the two planes of a frame's G-buffer inside one allocation (rt_kernels.cuh)
+rtd::GBuf gbuf_planes(unsigned char* base, long long npx) { rtd::GBuf g; g.nt = (float4*)base; g.ml = (int*)(base + (size_t)npx * sizeof(float4)); return g; }
 PaperKernel paper_kernel_of(const rt_scene* s) {
     const bool mm = s->hdr.cull_words != 0;
     return s->clustered ? (s->fits_const ? rtd::paper_gbuffer_kernel<true, true, false> : rtd::paper_gbuffer_kernel<false, true, false>)
@@ -594,15 +596,16 @@ int launch_frame(Context& cx, rt_scene* s, int mode, int rank, int world, uchar4
         const long long tiles = (npx + mt::kPixelsPerTile - 1) / mt::kPixelsPerTile;
         rc = ensure_mt_table(cx, tiles, rank, world); if (rc) return rc;
     } else {
-        rc = grow(&cx.d_gbuf, &cx.gbuf_cap, (size_t)npx * sizeof(rtd::GBuf)); if (rc) return rc;
+        rc = grow(&cx.d_gbuf, &cx.gbuf_cap, (size_t)npx * rtd::kGBufBytesPerPixel); if (rc) return rc;
     }
     rc = frame_begin(cx, st); if (rc) return rc;
     rc = bind_scene(cx, s, st); if (rc) return rc;
     CU(cudaMemsetAsync(cx.counters, 0, 4 * sizeof(unsigned long long), st));
     if (mode == RT_MODE_PAPER) {
         const unsigned blocks = (unsigned)((npx + 255) / 256);
-        paper_kernel_of(s)<<<blocks, 256, s->smem_bytes, st>>>(cx.d_gbuf, ids, cx.counters, rank, world);
-        rtd::paper_post_kernel<<<blocks, 256, 0, st>>>(cx.d_gbuf, rgba8, rgbf, rgb8, s->width, s->height, rank, world);
+        const rtd::GBuf gb = gbuf_planes(cx.d_gbuf, npx);
+        paper_kernel_of(s)<<<blocks, 256, s->smem_bytes, st>>>(gb, ids, cx.counters, rank, world);
+        rtd::paper_post_kernel<<<blocks, 256, 0, st>>>(gb, rgba8, rgbf, rgb8, s->width, s->height, rank, world);
         CU(cudaGetLastError());
         if (n_tiles_out) *n_tiles_out = (s->height + rtd::kPaperRows - 1) / rtd::kPaperRows;
         return frame_end(cx, st);
@@ -812,10 +815,10 @@ int rt_render_device(rt_scene* s, int mode, int rank, int world, void* rgba8_dev
 // ---- Paper frame without any allocation (rt_render_paper_device_noalloc) ----------------------------------------
 // Scratch of the entry point below: 256 bytes of device counters (cleared by every call), then the G-buffer of
 // paper_gbuffer_kernel / paper_post_kernel for at most RT_NOALLOC_MAX_PIXELS pixels.  The array lives in the module's
-// global segment of every device that loads the library (40 MiB, until the process exits).  In host code the name below
+// global segment of every device that loads the library (25 MiB, until the process exits).  In host code the name below
 // is only a stand-in for the symbol: the device address comes from cudaGetSymbolAddress, once per device.
 static constexpr size_t kNoAllocHead = 256;
-static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocHead + (size_t)RT_NOALLOC_MAX_PIXELS * sizeof(rtd::GBuf)];
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocHead + (size_t)RT_NOALLOC_MAX_PIXELS * rtd::kGBufBytesPerPixel];
 static unsigned char* g_noalloc_ptr[kMaxDevices] = {};      // device address of g_noalloc_scratch, per device ordinal
 
 namespace {
@@ -849,7 +852,7 @@ int rt_render_paper_device_noalloc(rt_scene* s, int rank, int world, void* rgba8
     unsigned char* scratch = nullptr;
     rc = noalloc_scratch(cx.device, &scratch); if (rc) return rc;
     auto* counters = (unsigned long long*)scratch;
-    auto* gbuf = (rtd::GBuf*)(scratch + kNoAllocHead);
+    const rtd::GBuf gbuf = gbuf_planes(scratch + kNoAllocHead, npx);
     cudaStream_t st = stream ? (cudaStream_t)stream : cx.stream;
     rc = frame_begin(cx, st); if (rc) return rc;
     rc = bind_scene(cx, s, st); if (rc) return rc;

@@ -32,7 +32,7 @@ constexpr float kInf = __builtin_huge_valf();
 // An interval end is (t, code): code = leaf | region<<20 | front<<23 | nmode<<24 | fallback<<26,
 // nmode 0 = geometric normal of the leaf at t, 1 = zero normal (csg.cpp:119), 2 = fallbacks[fallback].
 // Normals are evaluated lazily, only for the end that becomes the visible hit.
-struct Ivl { float t0, t1; uint32_t c0, c1; bool ok; };
+struct Ivl { float t0, t1; uint32_t c0, c1; int ok; };   // ok: 0 / 1 (an int: a bool member costs byte packing at every call boundary)
 constexpr uint32_t kFrontBit = 1u << 23;
 constexpr uint32_t kNModeMask = 3u << 24;
 

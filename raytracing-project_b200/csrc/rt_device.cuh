@@ -144,10 +144,18 @@ __device__ __forceinline__ V3 neg(V3 a) { return mk(-a.x, -a.y, -a.z); }
 __device__ __forceinline__ float dot(V3 a, V3 b) { return fmaf(a.x, b.x, fmaf(a.y, b.y, a.z * b.z)); }
 __device__ __forceinline__ V3 madd(V3 a, V3 d, float t) { return mk(fmaf(d.x, t, a.x), fmaf(d.y, t, a.y), fmaf(d.z, t, a.z)); }
 // Vec4::normalized (core.h:58-64): length <= 1e-6 falls back to (0,1,0)
+#ifndef RT_RSQRT
+#define RT_RSQRT 1          // length and reciprocal length from ONE MUFU.RSQ (sqrt is x * rsqrt(x) under -prec-sqrt=false anyway)
+#endif
 __device__ __forceinline__ V3 normalized(V3 a) {
     float l2 = dot(a, a);
+#if RT_RSQRT
+    const float inv = rsqrtf(l2);
+    if (l2 * inv > 1e-6f) return mk(a.x * inv, a.y * inv, a.z * inv);        // (l2 == 0: 0 * inf = NaN fails the test like L = 0)
+#else
     float L = sqrtf(l2);
     if (L > 1e-6f) { float inv = 1.0f / L; return mk(a.x * inv, a.y * inv, a.z * inv); }
+#endif
     return mk(0.f, 1.f, 0.f);
 }
 
@@ -226,16 +234,20 @@ __device__ __forceinline__ void cand_box_add(bool use, V3 v, int* lo, int* hi, i
 #define RT_CAND_NOINLINE 1        // one out-of-line copy of cand_build: camera and shadow masks share it (snorlax 4K 11.87 -> 11.35 ms)
 #endif
 #if RT_CAND_NOINLINE
-__device__ __noinline__ void cand_build(int b0, int nb, unsigned& tests) {
+__device__ __noinline__ unsigned cand_build(int b0, int nb) {
 #else
-__device__ __forceinline__ void cand_build(int b0, int nb, unsigned& tests) {
+__device__ __forceinline__ unsigned cand_build(int b0, int nb) {
 #endif
+    // (the number of bundle tests is RETURNED: a reference parameter of an out-of-line function pins the caller's whole
+    // counter struct to local memory, and every ++cnt.x in the kernel becomes a load and a store)
+    unsigned tests = 0;
     CandShared* S = cand_shared();
     const int W = c_hdr.cull_words, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
     const bool nan = b0 == 0 ? (S->nan_flags & 1) : (S->nan_flags & 2);
     float lo[3], hi[3];
+    const int* box_lo = b0 == 0 ? S->dir_lo : S->org_lo;            // (lo[3] and hi[3] are adjacent in both boxes)
 #pragma unroll
-    for (int k = 0; k < 3; ++k) { lo[k] = ord2f(b0 == 0 ? S->dir_lo[k] : S->org_lo[k]); hi[k] = ord2f(b0 == 0 ? S->dir_hi[k] : S->org_hi[k]); }
+    for (int k = 0; k < 3; ++k) { lo[k] = ord2f(box_lo[k]); hi[k] = ord2f(box_lo[3 + k]); }
     const bool empty = !(lo[0] <= hi[0]);                         // no ray contributed: nothing will be asked
     const float eps_max = __int_as_float(S->eps_max);
     Bundle B; B.wide = 1; B.t_hi = 0.f; B.h = 0.f; B.kd = 0.f; B.inv1md = 1.f; B.mx = B.my = B.mz = 0.f; B.cx = B.cy = B.cz = 0.f;
@@ -282,6 +294,7 @@ __device__ __forceinline__ void cand_build(int b0, int nb, unsigned& tests) {
         }
     }
     __syncthreads();
+    return tests;
 }
 // Candidate words of bundle b for the scans (nullptr: light beyond kMaxListLights, scanned without a mask).
 __device__ __forceinline__ const uint32_t* cand_of(int b) { return b <= kMaxListLights ? cand_words(b) : nullptr; }
@@ -519,6 +532,61 @@ template <bool C> __device__ __forceinline__ uint32_t candidates(const uint32_t*
     return cand;
 }
 
+// RT_OP_COMBINE_SPHERES: acc = (...(acc op s[first]) op s[first + 1]) ...) over n consecutive plain-sphere leaves.  OP >= 0:
+// the operation is known at compile time (csg is ignored).
+#ifndef RT_CSG_UNION_FOLD
+#define RT_CSG_UNION_FOLD 1
+#endif
+#ifndef RT_FOLD_COLD
+#define RT_FOLD_COLD 0           // A/B: 1 = the generic fold (intersection / difference) out of line
+#endif
+template <bool C, int OP>
+__device__ __forceinline__ void fold_spheres(Ivl& acc, int csg_rt, int first, int n, V3 o, V3 d, const uint32_t* leafw, unsigned& tests) {
+    const int csg = OP >= 0 ? OP : csg_rt;
+    for (int c0 = 0; c0 < n; c0 += 32) {
+        const int cnt = min(32, n - c0), base = first + c0;
+        // (leaf intervals live on the whole line, csg.cpp:61-163: the leaf bits were culled without a window)
+        uint32_t mask = candidates<C>(leafw, base, SV<C>::leaf_ptr(base), cnt, o, d, tests);
+        int pos = 0;
+        for (;;) {
+            const int k = mask ? (__ffs(mask) - 1) : cnt;          // next candidate, or the end of the chunk
+            float4 g = make_float4(0.f, 0.f, 0.f, 0.f); float hb = 0.f, disc = 0.f;
+            if (k < cnt) {
+                mask &= mask - 1; ++tests;
+                g = SV<C>::leaf_geom(base + k);
+                disc = sphere_disc(g, o, d, hb);
+                if (disc < 0.f) continue;                          // the mask is conservative: k is a miss like pos..k-1
+            }
+            // ---- spheres pos..k-1 are missed: the one-child case of csg_combine, applied in order ----
+            if (k > pos && acc.ok) {
+                if (csg == RT_CSG_INTERSECTION) acc.ok = false;
+                else if (isfinite(acc.t0) && isfinite(acc.t1) && acc.t0 <= acc.t1) origin_rewrite(acc);   // idempotent
+                else {
+                    Ivl none; none.ok = false; none.t0 = none.t1 = 0.f; none.c0 = none.c1 = 0;
+                    for (int m = pos; m < k && acc.ok; ++m) {
+                        if (isfinite(acc.t0) && isfinite(acc.t1) && acc.t0 <= acc.t1) origin_rewrite(acc);
+                        else acc = csg_combine(csg, acc, none);
+                    }
+                }
+            }
+            if (k >= cnt) break;
+            pos = k + 1;
+            const float sq = sqrtf(disc), ir = 1.f / g.w;
+            const bool xformed = (SV<C>::leaf_meta(base + k).x >> 8) & RT_FLAG_XFORMED;
+            Ivl b; b.ok = true; b.t0 = -hb - sq; b.t1 = -hb + sq;
+            b.c0 = b.c1 = (uint32_t)(base + k);
+            if (xformed ? (sq != 0.f) : (-sq * ir < 0.f)) b.c0 |= kFrontBit;
+            if (xformed ? (sq != 0.f) : (sq * ir < 0.f)) b.c1 |= kFrontBit;
+            acc = csg_combine(csg, acc, b);
+        }
+    }
+}
+
+template <bool C>
+__device__ __noinline__ void fold_spheres_cold(Ivl& acc, int csg, int first, int n, V3 o, V3 d, const uint32_t* leafw, unsigned& tests) {
+    fold_spheres<C, -1>(acc, csg, first, n, o, d, leafw, tests);
+}
+
 // `leafw`: the round's candidate words of the CSG leaves (section of the bundle's mask), or nullptr.
 template <bool C> __device__ __noinline__ ProgResult run_program(int first, int count, V3 o, V3 d, const uint32_t* leafw) {
     unsigned tests = 0;
@@ -535,43 +603,11 @@ template <bool C> __device__ __noinline__ ProgResult run_program(int first, int 
             case RT_OP_XFIX: xfix(acc, arg); break;
             case RT_OP_COMBINE_SPHERES: {            // acc = (...(acc op s[first]) op s[first+1]) ... ) over plain spheres
                 const int first = (int)(arg & 0x3FFFu), n = (int)(arg >> 14);
-                for (int c0 = 0; c0 < n; c0 += 32) {
-                    const int cnt = min(32, n - c0), base = first + c0;
-                    // (leaf intervals live on the whole line, csg.cpp:61-163: the leaf bits were culled without a window)
-                    uint32_t mask = candidates<C>(leafw, base, SV<C>::leaf_ptr(base), cnt, o, d, tests);
-                    int pos = 0;
-                    for (;;) {
-                        const int k = mask ? (__ffs(mask) - 1) : cnt;          // next candidate, or the end of the chunk
-                        float4 g = make_float4(0.f, 0.f, 0.f, 0.f); float hb = 0.f, disc = 0.f;
-                        if (k < cnt) {
-                            mask &= mask - 1; ++tests;
-                            g = SV<C>::leaf_geom(base + k);
-                            disc = sphere_disc(g, o, d, hb);
-                            if (disc < 0.f) continue;                          // the mask is conservative: k is a miss like pos..k-1
-                        }
-                        // ---- spheres pos..k-1 are missed: the one-child case of csg_combine, applied in order ----
-                        if (k > pos && acc.ok) {
-                            if (csg == RT_CSG_INTERSECTION) acc.ok = false;
-                            else if (isfinite(acc.t0) && isfinite(acc.t1) && acc.t0 <= acc.t1) origin_rewrite(acc);   // idempotent
-                            else {
-                                Ivl none; none.ok = false; none.t0 = none.t1 = 0.f; none.c0 = none.c1 = 0;
-                                for (int m = pos; m < k && acc.ok; ++m) {
-                                    if (isfinite(acc.t0) && isfinite(acc.t1) && acc.t0 <= acc.t1) origin_rewrite(acc);
-                                    else acc = csg_combine(csg, acc, none);
-                                }
-                            }
-                        }
-                        if (k >= cnt) break;
-                        pos = k + 1;
-                        const float sq = sqrtf(disc), ir = 1.f / g.w;
-                        const bool xformed = (SV<C>::leaf_meta(base + k).x >> 8) & RT_FLAG_XFORMED;
-                        Ivl b; b.ok = true; b.t0 = -hb - sq; b.t1 = -hb + sq;
-                        b.c0 = b.c1 = (uint32_t)(base + k);
-                        if (xformed ? (sq != 0.f) : (-sq * ir < 0.f)) b.c0 |= kFrontBit;
-                        if (xformed ? (sq != 0.f) : (sq * ir < 0.f)) b.c1 |= kFrontBit;
-                        acc = csg_combine(csg, acc, b);
-                    }
-                }
+                // (the union fold — a model built from spheres — gets its own copy with the operation known at compile time:
+                // csg_combine's case analysis collapses to a third)
+                if (RT_CSG_UNION_FOLD && csg == RT_CSG_UNION) fold_spheres<C, RT_CSG_UNION>(acc, csg, first, n, o, d, leafw, tests);
+                else if (RT_FOLD_COLD) fold_spheres_cold<C>(acc, csg, first, n, o, d, leafw, tests);
+                else fold_spheres<C, -1>(acc, csg, first, n, o, d, leafw, tests);
             } break;
         }
     }

@@ -165,7 +165,7 @@ __device__ __forceinline__ const uint32_t* camera_mask(bool active, V3 d, Counte
     CandShared* S = cand_shared();
     cand_box_add(active, d, S->dir_lo, S->dir_hi, &S->nan_flags, 1);
     __syncthreads();
-    cand_build(0, 1, cnt.tests);
+    cnt.tests += cand_build(0, 1);
     if (threadIdx.x < 3) { S->dir_lo[threadIdx.x] = kOrdPosInf; S->dir_hi[threadIdx.x] = kOrdNegInf; }     // for the next round
     if (threadIdx.x == 3) atomicAnd(&S->nan_flags, ~1);
     return cand_of(0);
@@ -213,8 +213,14 @@ constexpr int kRenderThreads = 256;
 
 // F ("flat"): no ray of the scene can spawn a child, see ray_step.  M: round-level masks (rt_device.cuh cand_*): the tile
 // is walked in CTA-wide rounds with barriers; kernels without M contain none of that code.
+// Scenes whose rays spawn children and that have no clustered runs (!F, !K: the explicit recursion stack and both scans
+// inlined) are register-starved at 64: they run 3 CTAs per SM with 80 registers (snorlax 4K with a reflective belly
+// 13.05 -> 12.23 ms; flat and clustered scenes lose 6-7 % at 3).
+#ifndef RT_NONFLAT_BLOCKS
+#define RT_NONFLAT_BLOCKS 3
+#endif
 template <bool C, bool K, bool F, bool M>
-__global__ void __launch_bounds__(kRenderThreads, RT_MIN_BLOCKS) render_standard_kernel(RenderParams prm) {
+__global__ void __launch_bounds__(kRenderThreads, (!F && !K) ? RT_NONFLAT_BLOCKS : RT_MIN_BLOCKS) render_standard_kernel(RenderParams prm) {
     // raw generator words: [0, kN) the tile's checkpoint, then the 8 blocks it yields (tempered on use)
     __shared__ __align__(16) uint32_t raw[mt::kN + mt::kOutputsPerTile];
     __shared__ __align__(16) unsigned char s_rgb[3 * mt::kPixelsPerTile];      // the tile's packed RGB8 (host-direct output)
@@ -242,7 +248,7 @@ __global__ void __launch_bounds__(kRenderThreads, RT_MIN_BLOCKS) render_standard
             for (int k = tid; k < mt::kN; k += kRenderThreads) raw[(b + 1) * mt::kN + k] = mt::next_word(raw + b * mt::kN, k);
             __syncthreads();
         }
-        if (M && RT_TILE_CAMERA_MASK) cand_build(0, 1, cnt.tests);         // the tile's camera mask (barrier inside)
+        if (M && RT_TILE_CAMERA_MASK) cnt.tests += cand_build(0, 1);         // the tile's camera mask (barrier inside)
         // --- one sample per thread; 8 consecutive lanes share a pixel.  With round-level culling the tile's 39 groups of 32
         // samples are dealt statically, 8 groups = 32 neighbouring pixels per round: the CTA walks a round together (camera
         // mask, camera rays, shadow masks, shadow rays; rt_trace.cuh).  Scenes too large for the masks take groups from a
@@ -523,18 +529,45 @@ __global__ void __launch_bounds__(kRenderThreads, RT_WAVE_BLOCKS) render_wavefro
 // ---------------------------------------------------------------------------------------------------
 // Paper mode.  The reference re-traces the centre ray and its 4 neighbours for every pixel
 // (tracer.cpp:133-178: 6 closest-hit scans per pixel); a G-buffer removes the 5 redundant ones.
-struct GBuf { float t, nx, ny, nz; int mat; float lum; int code; int hit; };   // 32 B
+//
+// G-buffer: 20 B per pixel in two planes (it is written once and read ~once from HBM, the only traffic of paper mode):
+//   nt[q] = (n.xyz, t)   float4, t = -1 for a miss (a hit has t >= 1e-4): what get_edge_strength compares between neighbours
+//   ml[q] = (material + 1) << 3 | hatch level   the cross-hatch thresholds of apply_crosshatch (tracer.cpp:188-205) depend on
+//           the pixel's luminance only, so pass 1 stores the 3-bit result of those float comparisons instead of the float.
+// (A first version kept 32 B per pixel: t, n, material, luminance, id, hit.)
+struct GBuf { float4* nt; int* ml; };
+constexpr int kGBufBytesPerPixel = 20;
 
 // rows owned by a rank: blocks of kPaperRows rows, interleaved; halo rows are recomputed locally
 constexpr int kPaperRows = 16;
 __device__ __host__ __forceinline__ bool paper_row_owned(int y, int rank, int world) { return ((y / kPaperRows) % world) == rank; }
+
+// apply_crosshatch (tracer.cpp:188-205), split: the luminance thresholds (pass 1) ...
+__device__ __forceinline__ int hatch_level(float L) {
+    if (L < 0.15f) return 0;
+    const float dark = 1.f - L;
+    return dark > 0.8f ? 1 : dark > 0.65f ? 2 : dark > 0.5f ? 3 : dark > 0.35f ? 4 : dark > 0.2f ? 5 : dark > 0.12f ? 6 : 7;
+}
+// ... and the line pattern of a level at pixel (x, y) (pass 2); C++ % keeps the sign of the dividend, as does CUDA's
+__device__ __forceinline__ float crosshatch(int level, int x, int y) {
+    if (level == 0) return 0.f;
+    const bool d1 = ((x + y) % 4) < 1, d2 = ((x - y) % 4) < 1, hz = (y % 4) < 1;
+    bool line = false;
+    if (level == 1)      line = (d1 && d2) || hz;
+    else if (level == 2) line = (d1 && d2) || (hz && ((x + y) % 3 == 0));
+    else if (level == 3) line = (d1 && d2) || (hz && ((x + y) % 4 == 0));
+    else if (level == 4) line = d1 || (hz && ((x + y) % 3 == 0));
+    else if (level == 5) line = d1;
+    else if (level == 6) line = d1 && ((x + y) % 8) < 2;
+    return line ? 0.f : 1.f;
+}
 
 // 3 CTAs per SM (80 registers): penguin 4K 1.17 -> 1.12 ms, snorlax 4K --paper 2.26 -> 2.05 ms; 4 (64 registers) spills back to 1.16 / 2.20
 #ifndef RT_PAPER_BLOCKS
 #define RT_PAPER_BLOCKS 3
 #endif
 template <bool C, bool K, bool M>
-__global__ void __launch_bounds__(256, RT_PAPER_BLOCKS) paper_gbuffer_kernel(GBuf* gb, int* ids, unsigned long long* counters, int rank, int world) {
+__global__ void __launch_bounds__(256, RT_PAPER_BLOCKS) paper_gbuffer_kernel(GBuf gb, int* ids, unsigned long long* counters, int rank, int world) {
     const int nx = c_hdr.nx, ny = c_hdr.ny;
     const long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     Counters cnt = {0, 0, 0, 0};
@@ -557,34 +590,17 @@ __global__ void __launch_bounds__(256, RT_PAPER_BLOCKS) paper_gbuffer_kernel(GBu
     const bool lit = hit && own && h.mat >= 0;
     const RGBf lum = shade<C, K, M>(lit, lists, h, madd(o, d, h.t), normalized(neg(d)), cnt);
     if (need) {
-        GBuf g;
-        g.hit = hit; g.t = hit ? h.t : kInf; g.mat = hit ? h.mat : -1; g.code = hit ? h.code : -1;
-        g.nx = hit ? h.n.x : 0.f; g.ny = hit ? h.n.y : 0.f; g.nz = hit ? h.n.z : 0.f;
         RGBf base = rgb(1.f, 1.f, 1.f);
         if (hit && own) base = lit ? lum : rgb(1.f, 0.f, 1.f);              // shading.cpp:33: magenta without a material
-        g.lum = 0.299f * base.r + 0.587f * base.g + 0.114f * base.b;      // tracer.cpp:123-125
-        gb[q] = g;
-        if (ids && own) ids[q] = g.code;
+        const float L = 0.299f * base.r + 0.587f * base.g + 0.114f * base.b;      // tracer.cpp:123-125
+        gb.nt[q] = hit ? make_float4(h.n.x, h.n.y, h.n.z, h.t) : make_float4(0.f, 0.f, 0.f, -1.f);
+        gb.ml[q] = ((hit ? h.mat : -1) + 1) << 3 | hatch_level(L);
+        if (ids && own) ids[q] = hit ? h.code : -1;
     }
     flush_counters(cnt, counters);
 }
 
-// apply_crosshatch (tracer.cpp:188-205); C++ % keeps the sign of the dividend, as does CUDA's
-__device__ __forceinline__ float crosshatch(float L, int x, int y) {
-    if (L < 0.15f) return 0.f;
-    const float dark = 1.f - L;
-    const bool d1 = ((x + y) % 4) < 1, d2 = ((x - y) % 4) < 1, hz = (y % 4) < 1;
-    bool line = false;
-    if (dark > 0.8f)       line = (d1 && d2) || hz;
-    else if (dark > 0.65f) line = (d1 && d2) || (hz && ((x + y) % 3 == 0));
-    else if (dark > 0.5f)  line = (d1 && d2) || (hz && ((x + y) % 4 == 0));
-    else if (dark > 0.35f) line = d1 || (hz && ((x + y) % 3 == 0));
-    else if (dark > 0.2f)  line = d1;
-    else if (dark > 0.12f) line = d1 && ((x + y) % 8) < 2;
-    return line ? 0.f : 1.f;
-}
-
-__global__ void __launch_bounds__(256) paper_post_kernel(const GBuf* __restrict__ gb, uchar4* rgba8, float4* rgbf, unsigned char* rgb8,
+__global__ void __launch_bounds__(256) paper_post_kernel(GBuf gb, uchar4* rgba8, float4* rgbf, unsigned char* rgb8,
                                                          int nx, int ny, int rank, int world) {
     __shared__ __align__(16) unsigned char s_rgb[3 * 256];               // host-direct output: the block's packed RGB8
     __shared__ int s_any;
@@ -594,7 +610,9 @@ __global__ void __launch_bounds__(256) paper_post_kernel(const GBuf* __restrict_
     const bool own = q < npx && paper_row_owned(y, rank, world);
     if (rgb8) { if (threadIdx.x == 0) s_any = 0; __syncthreads(); }
     if (own) {
-    const GBuf c = gb[q];
+    const float4 c = __ldg(gb.nt + q);
+    const int cml = __ldg(gb.ml + q);
+    const bool chit = c.w >= 0.f;
     // get_edge_strength (tracer.cpp:133-178)
     const int dx[4] = {-1, 1, 0, 0}, dy[4] = {0, 0, -1, 1};
     float edge = 0.f; int valid = 0;
@@ -603,14 +621,16 @@ __global__ void __launch_bounds__(256) paper_post_kernel(const GBuf* __restrict_
         const int xn = x + dx[i], yn = y + dy[i];
         if (xn < 0 || xn >= nx || yn < 0 || yn >= ny) continue;
         ++valid;
-        const GBuf n = gb[(long long)yn * nx + xn];
-        if ((c.hit != 0) != (n.hit != 0)) { edge = fmaxf(edge, 0.9f); continue; }
-        if (c.hit && n.hit) {
-            const float mn = fminf(c.t, n.t), mx = fmaxf(c.t, n.t);
+        const long long qn = (long long)yn * nx + xn;
+        const float4 n = __ldg(gb.nt + qn);
+        const bool nhit = n.w >= 0.f;
+        if (chit != nhit) { edge = fmaxf(edge, 0.9f); continue; }
+        if (chit && nhit) {
+            const float mn = fminf(c.w, n.w), mx = fmaxf(c.w, n.w);
             if (mn > 1e-4f && mx / mn > 3.0f) edge = fmaxf(edge, 0.6f);
-            const float nd = fmaf(c.nx, n.nx, fmaf(c.ny, n.ny, c.nz * n.nz));
+            const float nd = fmaf(c.x, n.x, fmaf(c.y, n.y, c.z * n.z));
             if (nd < 0.2f) edge = fmaxf(edge, 0.5f);
-            if (c.mat != n.mat && nd < 0.7f) edge = fmaxf(edge, 0.3f);
+            if (nd < 0.7f && (cml >> 3) != (__ldg(gb.ml + qn) >> 3)) edge = fmaxf(edge, 0.3f);
         }
     }
     if (valid < 4) edge *= 0.5f;
@@ -618,7 +638,7 @@ __global__ void __launch_bounds__(256) paper_post_kernel(const GBuf* __restrict_
     if (edge > 0.8f) v = 0.f;                                              // tracer.cpp:268-278
     else if (edge > 0.5f) v = 0.2f;
     else {
-        v = crosshatch(c.lum, x, y);
+        v = crosshatch(cml & 7, x, y);
         if (edge > 0.3f) v *= (1.f - (edge - 0.3f) * 0.4f);
     }
     const unsigned char b = to_byte(v);

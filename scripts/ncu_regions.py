@@ -4,17 +4,17 @@ moves, local-memory traffic and control flow inside each region.  Input: ncu --p
 Usage: ncu_regions.py src.csv"""
 import csv, re, sys, collections
 REGIONS = [
-    ("tile prologue: MT19937 twists, checkpoint load", [("rt_kernels.cuh", 166, 185), ("mt19937.cuh", 1, 999)]),
-    ("round: sample set-up, jitter, camera ray (FP64)", [("rt_kernels.cuh", 186, 217), ("rt_kernels.cuh", 106, 131)]),
-    ("round: resolve + store", [("rt_kernels.cuh", 218, 234)]),
-    ("round masks: box reduce + cand_build + bundle tests", [("rt_device.cuh", 156, 262), ("rt_cull.cuh", 1, 999), ("rt_kernels.cuh", 133, 144), ("device_atomic_functions.hpp", 1, 9999)]),
+    ("tile prologue: MT19937 twists, checkpoint load", [("rt_kernels.cuh", 229, 245), ("mt19937.cuh", 1, 999), ("rt_kernels.cuh", 184, 205)]),
+    ("round: sample set-up, jitter, camera ray (FP64)", [("rt_kernels.cuh", 260, 291), ("rt_kernels.cuh", 114, 128)]),
+    ("round: resolve + store", [("rt_kernels.cuh", 292, 312), ("rt_kernels.cuh", 130, 160)]),
+    ("round masks: box reduce + cand_build + bundle tests", [("rt_device.cuh", 165, 295), ("rt_cull.cuh", 1, 999), ("rt_kernels.cuh", 162, 172), ("device_atomic_functions.hpp", 1, 9999)]),
     ("scan loop (masked / run-based) + scan glue", [("rt_trace.cuh", 68, 207)]),
-    ("sphere_t / plane_t / sphere_disc / sphere_mask", [("rt_device.cuh", 263, 366)]),
-    ("generic_hit + run_program + leaf_interval + csg", [("rt_trace.cuh", 15, 67), ("rt_device.cuh", 367, 548), ("rt_csg.cuh", 1, 999)]),
+    ("sphere_t / plane_t / sphere_disc / sphere_mask", [("rt_device.cuh", 297, 399)]),
+    ("generic_hit + run_program + leaf_interval + csg", [("rt_trace.cuh", 15, 67), ("rt_device.cuh", 400, 582), ("rt_csg.cuh", 1, 999)]),
     ("closest_hit finalise (normal, material, code)", [("rt_trace.cuh", 208, 257)]),
-    ("shade loop + light_vector + light_shade", [("rt_trace.cuh", 258, 350)]),
-    ("ray_step / trace (recursion glue)", [("rt_trace.cuh", 351, 470)]),
-    ("vector helpers (dot, madd, normalized, SV accessors)", [("rt_device.cuh", 60, 155)]),
+    ("shade loop + light_vector + light_shade", [("rt_trace.cuh", 258, 390)]),
+    ("ray_step / trace (recursion glue)", [("rt_trace.cuh", 391, 510)]),
+    ("vector helpers (dot, madd, normalized, SV accessors)", [("rt_device.cuh", 60, 164)]),
 ]
 CLASS = {"fp32": {"FFMA", "FMUL", "FADD", "FSETP", "FSEL", "FMNMX", "FMNMX3", "MUFU", "FCHK", "FFMA2", "FMUL2", "FADD2"},
          "fp64": {"DFMA", "DMUL", "DADD", "DSETP", "F2F", "I2F", "F2I", "DMNMX"},

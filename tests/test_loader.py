@@ -113,3 +113,23 @@ def test_material_rules(rt):                             # json_loader.cpp:83-12
     assert (m.shininess, m.ior, m.kd) == pytest.approx((7, 1.5, 1.0))   # kd/ks keys in JSON are ignored
     d = rt.load_scene_from_json_text(json.dumps(BASE)).materials()[0]
     assert (d.ks, d.kr, d.kt, d.shininess, d.ior) == (0, 0, 0, 1, 1)
+
+
+def test_number_syntax_is_parsed_like_a_correctly_rounding_reader(rt):
+    """scenes/number_syntax.json stresses the number grammar (exponents, -0, 30-digit mantissas, duplicate keys, escapes).
+    The reference reads doubles with nlohmann/json (strtod: correctly rounded), as does Python's json; the product's reader
+    must produce the same doubles, seen here through the float32 geometry and the double camera of the compiled scene."""
+    import os
+    import numpy as np
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "scenes", "number_syntax.json")
+    want = json.load(open(path))                          # duplicate keys: the last one wins, as in nlohmann::json
+    s = rt.load_scene_from_json(path)
+    assert (s.width, s.height) == (96, 72)                # round(2.0E+0 * 4.8e1), round(15e-1 * 4.8e1)  (camera.h:19-21)
+    o = s.objects()
+    sph = want["objects"][1]["sphere"]
+    assert sph["radius"] == 0.65
+    assert list(o[1].geom) == [float(np.float32(v)) for v in sph["position"] + [sph["radius"]]]
+    assert list(o[2].geom)[3] == float(np.float32(4.9999999999999994e-1))
+    assert list(o[0].geom)[:3] == [0.0, 1.0, 0.0]         # 123456789012345678901234567890e-29 normalised
+    lights = [s.desc.lights[i] for i in range(s.desc.n_lights)]
+    assert [float(v) for v in lights[1].intensity] == [float(np.float32(v)) for v in want["sources"][1]["intensity"]]

@@ -45,7 +45,10 @@ def test_oracle_band_equals_full_frame(oa, goldens):
     assert not band[: H - 20].any() and not band[H - 10:].any()
 
 
-@pytest.mark.parametrize("scene,mode", [("pokeballs_small", "standard"), ("quirks", "paper"), ("synthetic_b_small", "standard")])
+# number_syntax: exponents, -0, 30-digit mantissas, escapes, duplicate keys — the oracle port shares the product's JSON reader
+# (csrc/json_min.hpp), ref_driver parses with the reference's nlohmann/json: equal framebuffers mean equal numbers
+@pytest.mark.parametrize("scene,mode", [("pokeballs_small", "standard"), ("quirks", "paper"), ("synthetic_b_small", "standard"),
+                                        ("number_syntax", "standard"), ("number_syntax", "paper")])
 def test_oracle_matches_live_reference(oa, scene, mode):
     if not oa.have_ref():
         pytest.skip("oracle/_ref/ref_driver not built on this machine")
