@@ -296,8 +296,10 @@ __device__ __forceinline__ unsigned cand_build(int b0, int nb) {
     __syncthreads();
     return tests;
 }
-// Candidate words of bundle b for the scans (nullptr: light beyond kMaxListLights, scanned without a mask).
-__device__ __forceinline__ const uint32_t* cand_of(int b) { return b <= kMaxListLights ? cand_words(b) : nullptr; }
+// Bundle index b as the scans take it (-1: light beyond kMaxListLights, scanned without a mask).  The scans are handed the
+// INDEX, not a pointer: a generic 64-bit pointer into shared memory costs two registers across every scan, address-window
+// arithmetic at every out-of-line call and generic loads inside the callee; cand_words(b) is an immediate LDS offset.
+__device__ __forceinline__ int cand_id(int b) { return b <= kMaxListLights ? b : -1; }
 // Candidate bits of entries [first, first + n), n <= 32, of a word array (nullptr: all of them).
 __device__ __forceinline__ uint32_t cand_bits(const uint32_t* words, int first, int n) {
     const uint32_t all = n >= 32 ? 0xffffffffu : ((1u << n) - 1u);
@@ -524,10 +526,10 @@ template <bool C> __device__ Ivl leaf_interval(int li, V3 o, V3 d, unsigned& tes
 struct ProgResult { Ivl v; unsigned tests; };       // tests: primitives examined (returned by value: a reference would pin the caller's counter to memory)
 
 // Candidates among the n <= 32 consecutive sphere-like entries [first, first + n) of a mask section for THIS ray: the
-// round's candidate bits (words, or all of them without a mask), narrowed by the per-lane conservative mask over the mask
+// round's candidate bits (the leaf section of bundle lb's words, or all of them for lb = -1), narrowed by the per-lane conservative mask over the mask
 // table entries `masks` when many remain.  A superset of the entries whose exact discriminant is >= 0.
-template <bool C> __device__ __forceinline__ uint32_t candidates(const uint32_t* words, int first, const float4* masks, int n, V3 o, V3 d, unsigned& tests) {
-    uint32_t cand = cand_bits(words, first, n);
+template <bool C> __device__ __forceinline__ uint32_t candidates(int lb, int first, const float4* masks, int n, V3 o, V3 d, unsigned& tests) {
+    uint32_t cand = cand_bits(lb >= 0 ? cand_words(lb) + c_hdr.cull_leaf_word : nullptr, first, n);
     if (3 * __popc(cand) > n + 2) { tests += n; cand &= sphere_mask<C>(masks, n, o, d); }
     return cand;
 }
@@ -541,12 +543,12 @@ template <bool C> __device__ __forceinline__ uint32_t candidates(const uint32_t*
 #define RT_FOLD_COLD 0           // A/B: 1 = the generic fold (intersection / difference) out of line
 #endif
 template <bool C, int OP>
-__device__ __forceinline__ void fold_spheres(Ivl& acc, int csg_rt, int first, int n, V3 o, V3 d, const uint32_t* leafw, unsigned& tests) {
+__device__ __forceinline__ void fold_spheres(Ivl& acc, int csg_rt, int first, int n, V3 o, V3 d, int lb, unsigned& tests) {
     const int csg = OP >= 0 ? OP : csg_rt;
     for (int c0 = 0; c0 < n; c0 += 32) {
         const int cnt = min(32, n - c0), base = first + c0;
         // (leaf intervals live on the whole line, csg.cpp:61-163: the leaf bits were culled without a window)
-        uint32_t mask = candidates<C>(leafw, base, SV<C>::leaf_ptr(base), cnt, o, d, tests);
+        uint32_t mask = candidates<C>(lb, base, SV<C>::leaf_ptr(base), cnt, o, d, tests);
         int pos = 0;
         for (;;) {
             const int k = mask ? (__ffs(mask) - 1) : cnt;          // next candidate, or the end of the chunk
@@ -583,12 +585,12 @@ __device__ __forceinline__ void fold_spheres(Ivl& acc, int csg_rt, int first, in
 }
 
 template <bool C>
-__device__ __noinline__ void fold_spheres_cold(Ivl& acc, int csg, int first, int n, V3 o, V3 d, const uint32_t* leafw, unsigned& tests) {
-    fold_spheres<C, -1>(acc, csg, first, n, o, d, leafw, tests);
+__device__ __noinline__ void fold_spheres_cold(Ivl& acc, int csg, int first, int n, V3 o, V3 d, int lb, unsigned& tests) {
+    fold_spheres<C, -1>(acc, csg, first, n, o, d, lb, tests);
 }
 
-// `leafw`: the round's candidate words of the CSG leaves (section of the bundle's mask), or nullptr.
-template <bool C> __device__ __noinline__ ProgResult run_program(int first, int count, V3 o, V3 d, const uint32_t* leafw) {
+// `lb`: the bundle whose mask holds the round's candidate bits of the CSG leaves, or -1.
+template <bool C> __device__ __noinline__ ProgResult run_program(int first, int count, V3 o, V3 d, int lb) {
     unsigned tests = 0;
     Ivl acc; acc.ok = false; acc.t0 = acc.t1 = 0.f; acc.c0 = acc.c1 = 0;
     Ivl stack[RT_MAX_CSG_STACK]; int sp = 0;
@@ -605,9 +607,9 @@ template <bool C> __device__ __noinline__ ProgResult run_program(int first, int 
                 const int first = (int)(arg & 0x3FFFu), n = (int)(arg >> 14);
                 // (the union fold — a model built from spheres — gets its own copy with the operation known at compile time:
                 // csg_combine's case analysis collapses to a third)
-                if (RT_CSG_UNION_FOLD && csg == RT_CSG_UNION) fold_spheres<C, RT_CSG_UNION>(acc, csg, first, n, o, d, leafw, tests);
-                else if (RT_FOLD_COLD) fold_spheres_cold<C>(acc, csg, first, n, o, d, leafw, tests);
-                else fold_spheres<C, -1>(acc, csg, first, n, o, d, leafw, tests);
+                if (RT_CSG_UNION_FOLD && csg == RT_CSG_UNION) fold_spheres<C, RT_CSG_UNION>(acc, csg, first, n, o, d, lb, tests);
+                else if (RT_FOLD_COLD) fold_spheres_cold<C>(acc, csg, first, n, o, d, lb, tests);
+                else fold_spheres<C, -1>(acc, csg, first, n, o, d, lb, tests);
             } break;
         }
     }

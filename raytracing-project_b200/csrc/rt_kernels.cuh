@@ -160,15 +160,15 @@ __device__ __forceinline__ void flush_counters(const Counters& c, unsigned long 
 }
 
 // Round prologue, ALL threads of the CTA: reduce the box of the camera-ray directions of the threads with `active`, cull
-// the scene against the camera bundle (cand_build, barriers inside) and return the round's camera mask (nullptr: none).
-__device__ __forceinline__ const uint32_t* camera_mask(bool active, V3 d, Counters& cnt) {
+// the scene against the camera bundle (cand_build, barriers inside) and return the round's camera bundle (index 0).
+__device__ __forceinline__ int camera_mask(bool active, V3 d, Counters& cnt) {
     CandShared* S = cand_shared();
     cand_box_add(active, d, S->dir_lo, S->dir_hi, &S->nan_flags, 1);
     __syncthreads();
     cnt.tests += cand_build(0, 1);
     if (threadIdx.x < 3) { S->dir_lo[threadIdx.x] = kOrdPosInf; S->dir_hi[threadIdx.x] = kOrdNegInf; }     // for the next round
     if (threadIdx.x == 3) atomicAnd(&S->nan_flags, ~1);
-    return cand_of(0);
+    return 0;
 }
 
 // The camera mask of a whole TILE (render_standard_kernel): instead of reducing the directions of every round's rays (two
@@ -290,7 +290,7 @@ __global__ void __launch_bounds__(kRenderThreads, (!F && !K) ? RT_NONFLAT_BLOCKS
                 camera_ray(sx, sy, o, d);
             }
             {   // with masks all threads of the CTA make these calls (barriers inside); a thread without a sample keeps company
-                const uint32_t* cand0 = lists == kListsNone ? nullptr : RT_TILE_CAMERA_MASK ? cand_of(0) : camera_mask(active, d, cnt);
+                const int cand0 = lists == kListsNone ? -1 : RT_TILE_CAMERA_MASK ? 0 : camera_mask(active, d, cnt);
                 Hit ph; bool phit;
                 c = trace<C, K, M, F, RT_MAX_RECURSION>(active, lists, cand0, o, d, ph, phit, cnt);
                 if (active && prm.ids) prm.ids[((long long)yy * nx + x) * 8 + (j & 7)] = phit ? ph.code : -1;
@@ -456,9 +456,9 @@ __global__ void __launch_bounds__(kRenderThreads, RT_WAVE_BLOCKS) render_wavefro
                 RGBf c = rgb(0.f, 0.f, 0.f);
                 Hit ph; bool phit = false;
                 if (limit <= 0) {                                    // tracer.cpp:26: black, but the id buffer is still defined
-                    if (valid) { ++cnt.primary; if (prm.ids) phit = closest_hit<C, K, false>(o, d, 1e-4f, kInf, nullptr, ph, cnt); }
+                    if (valid) { ++cnt.primary; if (prm.ids) phit = closest_hit<C, K, false>(o, d, 1e-4f, kInf, -1, ph, cnt); }
                 } else {
-                    const uint32_t* cand0 = camera_pass ? camera_mask(valid, d, cnt) : nullptr;
+                    const int cand0 = camera_pass ? camera_mask(valid, d, cnt) : -1;
                     more = !ray_step<C, K, M, false>(valid, camera_pass, cand0, o, d, depth, sp + 2, c, ph, phit, cnt) && valid;
                 }
                 if (valid) {
@@ -584,7 +584,7 @@ __global__ void __launch_bounds__(256, RT_PAPER_BLOCKS) paper_gbuffer_kernel(GBu
     // the CTA's 256 pixels are one round: camera mask, centre rays, shadow masks, shadow rays (rt_trace.cuh)
     constexpr bool lists = M;
     if (M) cand_init();
-    const uint32_t* cand0 = lists ? camera_mask(need, d, cnt) : nullptr;
+    const int cand0 = lists ? camera_mask(need, d, cnt) : -1;
     bool hit = false;
     if (need) { ++cnt.primary; hit = closest_hit<C, K, M>(o, d, 1e-4f, kInf, cand0, h, cnt); }      // tracer.cpp:111-120
     const bool lit = hit && own && h.mat >= 0;
@@ -680,8 +680,8 @@ __global__ void __launch_bounds__(128) trace_rays_kernel(const double* rays, dou
     Counters cnt = {0, 0, 0, 0};
     Hit h; bool hit;
     if (!active) return;                         // (no barrier below: known-answer rays belong to no bundle)
-    const RGBf c = trace<C, K, false, false, RT_MAX_RECURSION>(true, false, nullptr, o, d, h, hit, cnt);
-    const bool occ = occluded<C, K, false>(o, d, 1e-3f, 5.0f, nullptr, cnt);
+    const RGBf c = trace<C, K, false, false, RT_MAX_RECURSION>(true, false, -1, o, d, h, hit, cnt);
+    const bool occ = occluded<C, K, false>(o, d, 1e-3f, 5.0f, -1, cnt);
     double* r = out + (size_t)i * 16;
     for (int k = 0; k < 16; ++k) r[k] = 0.0;
     r[0] = hit ? 1.0 : 0.0;

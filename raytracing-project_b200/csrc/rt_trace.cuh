@@ -3,8 +3,8 @@
 //
 // There is ONE scan body (closest hit and any hit), ONE light term and ONE recursion step; the per-thread kernel, the
 // wavefront kernel, paper mode and the known-answer kernel all inline the same code.  The scans are plain per-thread code
-// (callable from divergent code); what they take from the round-level culling (rt_cull.cuh, rt_device.cuh cand_*) is a
-// pointer to the candidate words of their bundle — `cand`, or nullptr for rays that belong to no bundle (secondary rays,
+// (callable from divergent code); what they take from the round-level culling (rt_cull.cuh, rt_device.cuh cand_*) is the
+// index of their bundle's candidate words — `cb`, or -1 for rays that belong to no bundle (secondary rays,
 // known-answer rays), which then scan every run with the per-lane conservative mask.  Only shade<LISTS = true> and the
 // kernels' round prologue contain CTA barriers (they build the masks) and must be reached by all threads of the CTA.
 #pragma once
@@ -16,9 +16,9 @@ namespace rtd {
 // Returns true and the hit parameter when object `i` is hit inside the caller's window.  `inclusive`
 // windows are [tmin,tmax] (sphere/plane/pokeball, geometry.cpp:26-28,99), CSG uses t<tmax
 // (csg.cpp:176), transform-wrapped objects tmin<t<tmax (transform.cpp:38).  For programs the entry
-// code and raw entry time are returned for the deferred normal.  leafw: candidate words of the CSG leaves, or nullptr.
+// code and raw entry time are returned for the deferred normal.  lb: the bundle whose candidate words cover the CSG leaves, or -1.
 template <bool C, bool K>
-__device__ __forceinline__ bool generic_hit(int i, V3 o, V3 d, float tmin, float tmax, const uint32_t* leafw, float& t_out,
+__device__ __forceinline__ bool generic_hit(int i, V3 o, V3 d, float tmin, float tmax, const int lb, float& t_out,
                                             uint32_t& code_out, float& tent_out, unsigned& tests) {
     const int4 m = SV<C>::template obj_meta_k<K>(i);
     const int kind = m.x & 0xff, flags = m.x >> 8;
@@ -39,7 +39,7 @@ __device__ __forceinline__ bool generic_hit(int i, V3 o, V3 d, float tmin, float
             const float sq = sqrtf(disc);
             if (-hb + sq < 0.f || -hb - sq > tmax) return false;
         }
-        const ProgResult pr = run_program<C>(m.z, m.w, o, d, leafw);
+        const ProgResult pr = run_program<C>(m.z, m.w, o, d, lb);
         const Ivl v = pr.v; tests += pr.tests;
         if (!v.ok) return false;
         t = fmaxf(v.t0, lo);                                                 // csg.cpp:175-176
@@ -75,10 +75,10 @@ struct ScanResult { int best; float t; uint32_t code; float tent; };
 // (1) A ray of a round's bundle (camera rays, their shadow rays): the candidates are the set bits of the round's mask
 // `cand` (rt_device.cuh cand_build) — objects in device order, then the CSG leaves.  A handful of bits per query.
 template <bool C, bool K>
-__device__ __forceinline__ void scan_masked(V3 o, V3 d, float tmin, float tmax, const bool any, const uint32_t* cand, ScanResult& res, unsigned& tests) {
+__device__ __forceinline__ void scan_masked(V3 o, V3 d, float tmin, float tmax, const bool any, const int cb, ScanResult& res, unsigned& tests) {
     int best = -1; float best_t = tmax; uint32_t best_code = 0; float best_tent = 0.f;
     const int W = c_hdr.cull_leaf_word;
-    const uint32_t* leafw = cand + W;
+    const uint32_t* cand = cand_words(cb);
     for (int w = 0; w < W; ++w) {
         uint32_t bits = cand[w];
         while (bits) {
@@ -95,7 +95,7 @@ __device__ __forceinline__ void scan_masked(V3 o, V3 d, float tmin, float tmax, 
                 best = i; best_t = t;
             } else {
                 float tent; uint32_t code;
-                if (!generic_hit<C, K>(i, o, d, tmin, best_t, leafw, t, code, tent, tests)) continue;
+                if (!generic_hit<C, K>(i, o, d, tmin, best_t, cb, t, code, tent, tests)) continue;
                 best = i; best_t = t; best_code = code; best_tent = tent;
             }
             if (any) goto done;
@@ -170,7 +170,7 @@ __device__ __forceinline__ void scan_body(V3 o, V3 d, float tmin, float tmax, co
                 while (mask) {
                     const int i = c0 + __ffs(mask) - 1; mask &= mask - 1;
                     float t, tent; uint32_t code;
-                    if (generic_hit<C, K>(i, o, d, tmin, best_t, nullptr, t, code, tent, tests)) {
+                    if (generic_hit<C, K>(i, o, d, tmin, best_t, -1, t, code, tent, tests)) {
                         best = i; best_t = t; best_code = code; best_tent = tent;
                         if (any) goto done;
                     }
@@ -197,18 +197,32 @@ __device__ __noinline__ ScanOut scan_shared(V3 o, V3 d, float tmin, float tmax, 
 #ifndef RT_SCAN_SHARED
 #define RT_SCAN_SHARED 0          // A/B: 1 = the out-of-line scan for every scene
 #endif
+// A/B build switch: 1 = ONE out-of-line copy of the masked scan serves closest hit and any hit (the callee gets a fresh
+// register budget and the callers' loop nests lose a level of convergence barriers; the call costs a spill of the caller's state)
+#ifndef RT_MASKED_CALL
+#define RT_MASKED_CALL 0
+#endif
+template <bool C, bool K>
+__device__ __noinline__ ScanOut scan_masked_shared(V3 o, V3 d, float tmin, float tmax, bool any, int cb) {
+    ScanOut out; out.tests = 0;
+    scan_masked<C, K>(o, d, tmin, tmax, any, cb, out.r, out.tests);
+    return out;
+}
 // M: the kernel was built with round-level masks (rt_device.cuh); kernels without them contain none of that code.
 template <bool C, bool K, bool M, bool ANY>
-__device__ __forceinline__ void scan(V3 o, V3 d, float tmin, float tmax, const uint32_t* cand, ScanResult& res, Counters& cnt) {
-    if (M && cand) scan_masked<C, K>(o, d, tmin, tmax, ANY, cand, res, cnt.tests);
+__device__ __forceinline__ void scan(V3 o, V3 d, float tmin, float tmax, const int cb, ScanResult& res, Counters& cnt) {
+    if (M && cb >= 0) {
+        if (RT_MASKED_CALL) { const ScanOut so = scan_masked_shared<C, K>(o, d, tmin, tmax, ANY, cb); res = so.r; cnt.tests += so.tests; }
+        else scan_masked<C, K>(o, d, tmin, tmax, ANY, cb, res, cnt.tests);
+    }
     else if (K || RT_SCAN_SHARED) { const ScanOut so = scan_shared<C, K>(o, d, tmin, tmax, ANY); res = so.r; cnt.tests += so.tests; }
     else scan_body<C, K>(o, d, tmin, tmax, ANY, res, cnt.tests);
 }
 
 template <bool C, bool K, bool M>
-__device__ __forceinline__ bool closest_hit(V3 o, V3 d, float tmin, float tmax, const uint32_t* cand, Hit& hit, Counters& cnt) {
+__device__ __forceinline__ bool closest_hit(V3 o, V3 d, float tmin, float tmax, const int cb, Hit& hit, Counters& cnt) {
     ScanResult sr;
-    scan<C, K, M, false>(o, d, tmin, tmax, cand, sr, cnt);
+    scan<C, K, M, false>(o, d, tmin, tmax, cb, sr, cnt);
     const int best = sr.best;
     if (best < 0) return false;
     // ---- finalise the winner: normal, front_face, material, id code ----
@@ -249,9 +263,9 @@ __device__ __forceinline__ bool closest_hit(V3 o, V3 d, float tmin, float tmax, 
 }
 
 template <bool C, bool K, bool M>
-__device__ __forceinline__ bool occluded(V3 o, V3 d, float tmin, float tmax, const uint32_t* cand, Counters& cnt) {
+__device__ __forceinline__ bool occluded(V3 o, V3 d, float tmin, float tmax, const int cb, Counters& cnt) {
     ScanResult sr;
-    scan<C, K, M, true>(o, d, tmin, tmax, cand, sr, cnt);
+    scan<C, K, M, true>(o, d, tmin, tmax, cb, sr, cnt);
     return sr.best >= 0;
 }
 
@@ -347,7 +361,8 @@ __device__ __forceinline__ RGBf shade(bool lit, const int LISTS, const Hit& h, V
     RGBf E = rgb(0.f, 0.f, 0.f);
     if (lists != kListsWarp && !lit) return E;
     if (lit) { const float4 m1 = material(h.mat, 1); E = rgb(m1.x, m1.y, m1.z); }       // ambient (x) scene ambient, pre-multiplied
-    uint32_t* my_words = lists == kListsWarp ? cand_words(1 + (int)(threadIdx.x >> 5)) : nullptr;
+    const int my_bundle = 1 + (int)(threadIdx.x >> 5);                      // kListsWarp: the warp's own mask slot
+    uint32_t* my_words = lists == kListsWarp ? cand_words(my_bundle) : nullptr;
     for (int l0 = 0; l0 < nl; l0 += 32) {
         const int cnt_l = min(32, nl - l0);
         uint32_t vis = 0;
@@ -357,7 +372,7 @@ __device__ __forceinline__ RGBf shade(bool lit, const int LISTS, const Hit& h, V
             const float ndotl = light_vector(lp, p, h.n, wi, dist);
             const float tmaxS = dist - eps;
             const bool need = lit && !(ndotl <= 0.f) && !(tmaxS <= eps);     // shading.cpp:51,94 / :98
-            const uint32_t* cand = nullptr;
+            int cb = -1;                                                     // bundle whose mask serves this light (-1: none)
             if (lists == kListsWarp) {
                 if (!__any_sync(kFullWarp, need)) continue;                 // (warp-uniform)
                 if (bok) {
@@ -375,15 +390,15 @@ __device__ __forceinline__ RGBf shade(bool lit, const int LISTS, const Hit& h, V
                         if (lane == 0) my_words[w] = bits;
                     }
                     __syncwarp();
-                    cand = my_words;
+                    cb = my_bundle;
                 }
             } else {
                 if (!need) continue;
-                if (lists == kListsCta) cand = cand_of(1 + l0 + k);
+                if (lists == kListsCta) cb = cand_id(1 + l0 + k);
             }
             if (need) {
                 ++cnt.shadow;
-                if (!occluded<C, K, M>(so, normalized(wi), eps, tmaxS, cand, cnt)) vis |= 1u << k;   // Ray ctor re-normalises (core.h:278)
+                if (!occluded<C, K, M>(so, normalized(wi), eps, tmaxS, cb, cnt)) vis |= 1u << k;   // Ray ctor re-normalises (core.h:278)
             }
             if (lists == kListsWarp) __syncwarp();                          // the words are rewritten for the next light
         }
@@ -410,13 +425,13 @@ __device__ __forceinline__ RGBf shade(bool lit, const int LISTS, const Hit& h, V
 // recursion == 1): no frames are touched and every tree finishes with its first ray.  LISTS: the ray is a camera ray of
 // a round — `cand` is the round's mask of the camera bundle, ALL threads of the CTA make the call (see shade).
 template <bool C, bool K, bool M, bool FLAT>
-__device__ __forceinline__ bool ray_step(bool alive, const int LISTS, const uint32_t* cand, V3& o, V3& d, int& sp, float4* __restrict__ frames,
+__device__ __forceinline__ bool ray_step(bool alive, const int LISTS, const int cb, V3& o, V3& d, int& sp, float4* __restrict__ frames,
                                          RGBf& result, Hit& primary, bool& primary_hit, Counters& cnt) {
     const int limit = c_hdr.recursion;
     Hit h; h.mat = -1; h.t = 0.f; h.n = mk(0.f, 1.f, 0.f); h.front = true; h.code = -1;
     bool hit = false;
     if (alive) {
-        hit = closest_hit<C, K, M>(o, d, 1e-4f, kInf, cand, h, cnt);       // tracer.cpp:29
+        hit = closest_hit<C, K, M>(o, d, 1e-4f, kInf, cb, h, cnt);         // tracer.cpp:29
         if (FLAT || LISTS || sp == 0) { ++cnt.primary; primary = h; primary_hit = hit; } else ++cnt.secondary;
     }
     const V3 p = madd(o, d, h.t);
@@ -492,23 +507,23 @@ __device__ __forceinline__ bool ray_step(bool alive, const int LISTS, const uint
 // available = deepest recursion served.  LISTS: the sample is a camera ray of a round whose camera-bundle mask is `cand`;
 // ALL threads of the CTA make the call (the first ray and its shadow rays use the round's masks, deeper rays none).
 template <bool C, bool K, bool M, bool FLAT, int D>
-__device__ __forceinline__ RGBf trace(bool active, const int LISTS, const uint32_t* cand, V3 o, V3 d, Hit& primary, bool& primary_hit, Counters& cnt) {
+__device__ __forceinline__ RGBf trace(bool active, const int LISTS, const int cb, V3 o, V3 d, Hit& primary, bool& primary_hit, Counters& cnt) {
     primary_hit = false;
     RGBf result = rgb(0.f, 0.f, 0.f);
     if (c_hdr.recursion <= 0) {                                              // tracer.cpp:26 at depth 0: black, ids still defined
-        if (active) { ++cnt.primary; primary_hit = closest_hit<C, K, M>(o, d, 1e-4f, kInf, cand, primary, cnt); }
+        if (active) { ++cnt.primary; primary_hit = closest_hit<C, K, M>(o, d, 1e-4f, kInf, cb, primary, cnt); }
         return result;
     }
     if (FLAT) {
         int sp = 0;
-        ray_step<C, K, M, true>(active, LISTS, cand, o, d, sp, nullptr, result, primary, primary_hit, cnt);
+        ray_step<C, K, M, true>(active, LISTS, cb, o, d, sp, nullptr, result, primary, primary_hit, cnt);
         return result;
     }
     float4 frames[3 * D];
     int sp = 0;                     // == depth of the ray being traced
     int lists = LISTS;              // the camera ray: all threads; deeper rays: the threads whose tree goes on, no masks
     for (;;) {
-        const bool done = ray_step<C, K, M, false>(active, lists, lists ? cand : nullptr, o, d, sp, frames, result, primary, primary_hit, cnt);
+        const bool done = ray_step<C, K, M, false>(active, lists, lists ? cb : -1, o, d, sp, frames, result, primary, primary_hit, cnt);
         if (!active || done) break;
         lists = kListsNone;
     }
