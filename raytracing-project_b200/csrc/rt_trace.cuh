@@ -360,15 +360,17 @@ __device__ __forceinline__ RGBf shade(bool lit, const int LISTS, const Hit& h, V
     }
     RGBf E = rgb(0.f, 0.f, 0.f);
     if (lists != kListsWarp && !lit) return E;
-    if (lit) { const float4 m1 = material(h.mat, 1); E = rgb(m1.x, m1.y, m1.z); }       // ambient (x) scene ambient, pre-multiplied
     const int my_bundle = 1 + (int)(threadIdx.x >> 5);                      // kListsWarp: the warp's own mask slot
     uint32_t* my_words = lists == kListsWarp ? cand_words(my_bundle) : nullptr;
-    for (int l0 = 0; l0 < nl; l0 += 32) {
-        const int cnt_l = min(32, nl - l0);
+    // One running light index l: a chunk is the lights [l & ~31, ...) that share the 32 visibility bits, so two registers
+    // (l, vis) stay alive across the scans; nothing of the shading (E, materials, wo's products) is live in pass 1.
+    int l = 0;
+    do {
         uint32_t vis = 0;
-        for (int k = 0; k < cnt_l; ++k) {
+        const int chunk_end = min(nl, (l | 31) + 1);
+        for (; l < chunk_end; ++l) {
             V3 wi; float dist;
-            const float4 lp = SV<C>::light(l0 + k, 0);
+            const float4 lp = SV<C>::light(l, 0);
             const float ndotl = light_vector(lp, p, h.n, wi, dist);
             const float tmaxS = dist - eps;
             const bool need = lit && !(ndotl <= 0.f) && !(tmaxS <= eps);     // shading.cpp:51,94 / :98
@@ -394,21 +396,24 @@ __device__ __forceinline__ RGBf shade(bool lit, const int LISTS, const Hit& h, V
                 }
             } else {
                 if (!need) continue;
-                if (lists == kListsCta) cb = cand_id(1 + l0 + k);
+                if (lists == kListsCta) cb = cand_id(1 + l);
             }
             if (need) {
                 ++cnt.shadow;
-                if (!occluded<C, K, M>(so, normalized(wi), eps, tmaxS, cb, cnt)) vis |= 1u << k;   // Ray ctor re-normalises (core.h:278)
+                if (!occluded<C, K, M>(so, normalized(wi), eps, tmaxS, cb, cnt)) vis |= 1u << (l & 31);   // Ray ctor re-normalises (core.h:278)
             }
             if (lists == kListsWarp) __syncwarp();                          // the words are rewritten for the next light
         }
         if (!lit) continue;
+        const int l0 = (l - 1) & ~31;                                        // first light of the chunk just queried
+        if (l0 == 0) { const float4 m1 = material(h.mat, 1); E = rgb(m1.x, m1.y, m1.z); }   // ambient (x) scene ambient, pre-multiplied
         const float4 m0 = material(h.mat, 0), m2 = material(h.mat, 2);
         while (vis) {
             const int k = __ffs(vis) - 1; vis &= vis - 1;
             light_shade<C>(l0 + k, m0, m0.w, m2.y, m2.w, h.n, p, wo, E);
         }
-    }
+    } while (l < nl);
+    if (nl <= 0 && lit) { const float4 m1 = material(h.mat, 1); E = rgb(m1.x, m1.y, m1.z); }       // no lights: ambient only
     return rgb(fminf(1.5f, E.r), fminf(1.5f, E.g), fminf(1.5f, E.b));        // shading.cpp:133-135
 }
 
