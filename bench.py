@@ -154,6 +154,39 @@ def cpu_paper_frame(scene_path: str, width: int, height: int, shadow_rays: int |
     return {"value": rays / (ms * 1e-3) / 1e6, "busy_ms": ms, "rays": rays, "kind": "reference" if have_ref else "port"}
 
 
+L2_NOTE = "flushed between timed steps (256 MB memset)"
+
+
+def workload_config(scene_path: str, paper: bool, world: int, exchange: str | None = None) -> dict:
+    """`config` of the JSON line, derived from the scene file alone so that BOTH arms print the same object for the same
+    workload (the reference arm is "on your arm's config": the GPU-only keys describe the arm it is compared with)."""
+    with open(scene_path) as f:
+        sc = json.load(f)
+    scr = sc["screen"]
+    W = max(1, round(scr["dimensions"][0] * scr.get("dpi", 72))); H = max(1, round(scr["dimensions"][1] * scr.get("dpi", 72)))
+    prims = ("sphere", "halfSpace", "pokeball")
+
+    def leaves(node, inside):                     # primitives below a CSG node (the scene compiler's leaf count)
+        n = 0
+        for k, v in node.items():
+            if k in prims:
+                n += 1 if inside else 0
+            elif k in ("union", "intersection", "difference"):
+                n += sum(leaves(c, True) for c in v)
+            elif k == "csg":
+                n += leaves(v["left"], True) + leaves(v["right"], True)
+            elif k in ("translation", "scaling", "rotation"):
+                n += leaves(v["subject"], inside)
+        return n
+    if exchange is None:
+        exchange = "none (1 GPU)" if world == 1 else "peer stores into rank 0's frame over NVLink + 4-byte all-reduce"
+    return {"workload": os.path.basename(scene_path), "width": W, "height": H, "spp": 1 if paper else 8,
+            "mode": "paper" if paper else "standard", "recursion": int(sc.get("medium", {}).get("recursion", 5)),
+            "lights": len(sc.get("sources", [])), "objects": len(sc.get("objects", [])),
+            "csg_leaves": sum(leaves(o, False) for o in sc.get("objects", [])),
+            "parallelism": f"row-tile interleave x{world}", "exchange": exchange, "l2": L2_NOTE}
+
+
 def run_reference(args) -> None:
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -175,8 +208,8 @@ def run_reference(args) -> None:
             "impl": "reference", "metric": "Mrays/s", "value": v, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": len(vals),
             "warmup": min(args.warmup, 1), "ms_per_step": float(np.mean(ms)), "ms_per_frame": float(np.mean(ms)), "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": os.path.basename(args.scene), "width": W, "height": H, "spp": 1, "mode": "paper",
-                       "step": "one whole paper-mode frame, 1 thread (closest-hit queries only: 6 per pixel, tracer.cpp:133-178,262)"},
+            "config": workload_config(args.scene, True, args.gpus),
+            "reference_step": "one whole paper-mode frame, 1 thread (closest-hit queries only: 6 per pixel, tracer.cpp:133-178,262)",
             "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": 1, "kind": c["kind"], "sample": f"whole {W}x{H} paper frame"},
             "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
         return
@@ -193,9 +226,9 @@ def run_reference(args) -> None:
         "impl": "reference", "metric": "Mrays/s", "value": v, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": float(np.mean(step_ms)), "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": os.path.basename(args.scene), "width": W, "height": H, "spp": 8, "mode": "standard",
-                   "step": "bounded row sample of one frame (the reference cannot render a sub-frame faster than its RNG stream: rows "
-                           "are sampled with rng.discard, oracle/ref_driver.cpp), one single-threaded process per host core"},
+        "config": workload_config(args.scene, False, args.gpus),
+        "reference_step": "bounded row sample of one frame (the reference cannot render a sub-frame faster than its RNG stream: rows "
+                          "are sampled with rng.discard, oracle/ref_driver.cpp), one single-threaded process per host core",
         "ms_per_frame_extrapolated": frame_rays_est / (v * 1e6) * 1e3,
         "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": threads, "kind": last["kind"], "sample": sample},
         "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -432,10 +465,7 @@ def run_ours(args) -> None:
             "metric": "Mrays/s", "value": rays_per_frame / (ms_per_step * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "ms_per_frame": ms_per_step,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": os.path.basename(args.scene), "width": W, "height": H, "spp": 1 if args.paper else 8,
-                       "mode": "paper" if args.paper else "standard", "recursion": int(d.recursion), "lights": int(d.n_lights),
-                       "objects": int(d.n_objects), "csg_leaves": int(d.n_leaves), "parallelism": f"row-tile interleave x{world}", "exchange": exchange,
-                       "l2": "flushed between timed steps (256 MB memset)"},
+            "config": workload_config(args.scene, args.paper, world, exchange),
             "rays_per_frame": rays_per_frame, "rays": tot, "kernel_ms": kernel_ms,
             "e2e": {"value": rays_per_frame / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_frame": e2e_ms,
                     "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h_bytes), "path": e2e_path},

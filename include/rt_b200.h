@@ -280,8 +280,9 @@ int rt_debug_device_layout(const rt_scene_desc* desc, int* order, int* n_runs, i
  * pass masks4 = NULL to query n.                                                                              */
 int rt_debug_mask_table(const rt_scene_desc* desc, int* n, float* masks4, float* scale);
 
-/* Test hooks.  name: "flat", "cull", "wavefront", "global_scene" (kernel / data-path selection of scenes uploaded
- * afterwards; "cull" = 0 switches the round-level culling off: every ray scans every run) or "mt_sequential" (checkpoint table by the twist-by-twist walk); value -1 = the library's own choice,
+/* Test hooks.  name: "flat", "cull", "wavefront", "global_scene", "grid" (kernel / data-path selection of scenes uploaded
+ * afterwards; "cull" = 0 switches the round-level culling off: every ray scans every run; "grid" = 0 / 1: without / with the
+ * uniform grid for incoherent rays wherever one can be built) or "mt_sequential" (checkpoint table by the twist-by-twist walk); value -1 = the library's own choice,
  * 0 / 1 = forced off / on.  The library never reads its behaviour from the environment.                          */
 int rt_debug_set_option(const char* name, int value);
 

@@ -70,7 +70,7 @@ Context* g_ctxs[kMaxDevices] = {};        // created on demand (rt_init, rt_init
 Context* g_cur = nullptr;                 // the process's render device (rt_init)
 std::mutex g_mu;                          // guards g_ctxs / g_cur / the host-frame registry; taken BEFORE a context's mutex, never after
 // Test hooks (rt_debug_set_option): -1 = the library's own choice, 0 / 1 = forced.  Never read from the environment.
-struct DebugOptions { std::atomic<int> flat{-1}, cull{-1}, wavefront{-1}, global_scene{-1}, mt_sequential{-1}; };
+struct DebugOptions { std::atomic<int> flat{-1}, cull{-1}, wavefront{-1}, global_scene{-1}, mt_sequential{-1}, grid{-1}; };
 DebugOptions g_opts;                      // (atomics: read under a context's mutex, written under g_mu)
 constexpr size_t kSceneSmemBudget = 80 * 1024;   // + 25 KB of MT19937 buffers: two CTAs per SM still fit in 227 KB
 
@@ -88,6 +88,8 @@ struct rt_scene {
     std::vector<float4> obj_geom, leaf_geom, pokeballs, affines, materials, lights, fallbacks, clusters, masks, cull_geom;
     std::vector<uint32_t> cull_plane_bits;
     int cull_words{0}, cull_leaf_word{0};
+    rtd::GridHeader grid{};                // uniform grid over the plain spheres / pokeballs (rt_grid.cuh); words == 0: none
+    std::vector<uint32_t> grid_masks;
     float mask_scale{0.f};
     std::vector<int4> obj_meta, leaf_meta, runs;
     std::vector<int> obj_orig;
@@ -144,7 +146,7 @@ float4 bound_of(const rt_prim* objs, const int* idx, int n) {
     return make_float4((float)c[0], (float)c[1], (float)c[2], (float)(R * 1.002 + 1e-3));
 }
 
-void build_host_arrays(const rt_scene_desc& d, rt_scene& s) {
+void build_host_arrays(const rt_scene_desc& d, rt_scene& s, bool want_grid = false) {
     // device order of the top-level objects: JSON order, except inside clustered runs (see above)
     std::vector<int> order(d.n_objects);
     for (int i = 0; i < d.n_objects; ++i) order[i] = i;
@@ -247,6 +249,21 @@ void build_host_arrays(const rt_scene_desc& d, rt_scene& s) {
         s.runs.push_back(make_int4(kind, i, j - i, ctab));
         i = j;
     }
+    // Uniform grid (rt_grid.cuh) for scenes whose rays are mostly incoherent (the caller decides): every plain sphere /
+    // pokeball — all of them sit in unclustered runs here — is binned by its device index.  (The kernels stay the ones
+    // without bounds: the out-of-line scan of the K kernels costs this kind of scene 16 %.)
+    constexpr int kGridMinSpheres = 24;
+    if (want_grid && !s.clustered && d.n_objects <= 32 * rtd::kGridMaxWords) {
+        std::vector<float> sph; std::vector<int> bit;
+        for (size_t i = 0; i < s.obj_geom.size(); ++i) {
+            const int kind = s.obj_meta[i].x & 0xff, flags = s.obj_meta[i].x >> 8;
+            if (flags == 0 && (kind == RT_PRIM_SPHERE || kind == RT_PRIM_POKEBALL)) {
+                sph.insert(sph.end(), {s.obj_geom[i].x, s.obj_geom[i].y, s.obj_geom[i].z, s.obj_geom[i].w});
+                bit.push_back((int)i);
+            }
+        }
+        if ((int)bit.size() >= kGridMinSpheres) rtd::grid_build(sph.data(), bit.data(), (int)bit.size(), d.n_objects, s.grid, s.grid_masks);
+    }
     // Mask table of sphere_mask: (c, |c|^2 - r^2 - 2^-16 (|c|^2 + r^2)) for every entry of obj_geom | leaf_geom | clusters
     // (entries that are not sphere-like are never scanned through it): the primitive's own share of the scan's rounding
     // margin is folded into w, so the margin is per primitive.  `scale` = max(|c|^2 + r^2) is only reported.
@@ -292,8 +309,17 @@ void build_host_arrays(const rt_scene_desc& d, rt_scene& s) {
         s.cull_geom.push_back(plain ? make_float4(g.x, g.y, g.z, std::fabs(g.w)) : make_float4(0.f, 0.f, 0.f, inf));
     }
     pad32(); s.cull_words = (int)(s.cull_geom.size() / 32);
-    s.cull_plane_bits.assign((size_t)std::max(s.cull_words, 1), 0u);
+    // three bit planes of W = max(cull_words, 1) words each: [0, W) entry is culled as a plane; [W, 2W) object is a plain
+    // half-space (kind, whatever its normal's length); [2W, 3W) object is generic (CSG program, wrapped / affine primitive):
+    // the masked scans classify their candidates from these words instead of loading each candidate's meta record
+    const size_t Wc = (size_t)std::max(s.cull_words, 1);
+    s.cull_plane_bits.assign(3 * Wc, 0u);
     for (size_t i : planes) s.cull_plane_bits[i >> 5] |= 1u << (i & 31);
+    for (size_t i = 0; i < s.obj_meta.size(); ++i) {
+        const int kind = s.obj_meta[i].x & 0xff, flags = s.obj_meta[i].x >> 8;
+        if (flags == 0 && kind == RT_PRIM_HALFSPACE) s.cull_plane_bits[Wc + (i >> 5)] |= 1u << (i & 31);
+        if (flags != 0 || kind == RT_PRIM_PROGRAM) s.cull_plane_bits[2 * Wc + (i >> 5)] |= 1u << (i & 31);
+    }
 }
 
 
@@ -416,14 +442,20 @@ int upload_scene(Context& cx, const rt_scene_desc* d, rt_scene** out) {
     CU(cudaSetDevice(cx.device));
     auto* s = new rt_scene();
     s->cx = &cx;
-    build_host_arrays(*d, *s);
+    // bounce-heavy scenes (the wavefront kernel's): most rays are secondary rays that belong to no bundle -> uniform grid
+    int n_bounce0 = 0;
+    for (int i = 0; i < d->n_materials; ++i) n_bounce0 += (d->materials[i].kr > 0.f || d->materials[i].kt > 0.f) ? 1 : 0;
+    bool want_grid = d->recursion >= 2 && d->n_materials > 0 && 2 * n_bounce0 >= d->n_materials;
+    if (g_opts.wavefront.load() >= 0) want_grid = g_opts.wavefront.load() == 1;
+    if (g_opts.grid.load() >= 0) want_grid = g_opts.grid.load() == 1;       // test hook
+    build_host_arrays(*d, *s, want_grid);
     Blob blob;
     const size_t o_obj_geom = blob.add(s->obj_geom), o_obj_meta = blob.add(s->obj_meta), o_leaf_geom = blob.add(s->leaf_geom),
                  o_leaf_meta = blob.add(s->leaf_meta), o_pokeballs = blob.add(s->pokeballs), o_affines = blob.add(s->affines),
                  o_ops = blob.add(s->ops), o_materials = blob.add(s->materials), o_lights = blob.add(s->lights),
                  o_fallbacks = blob.add(s->fallbacks), o_runs = blob.add(s->runs), o_clusters = blob.add(s->clusters),
                  o_obj_orig = blob.add(s->obj_orig), o_masks = blob.add(s->masks), o_cull_geom = blob.add(s->cull_geom),
-                 o_cull_plane_bits = blob.add(s->cull_plane_bits);
+                 o_cull_plane_bits = blob.add(s->cull_plane_bits), o_grid_masks = blob.add(s->grid_masks);
     int rc = arena_take(cx, blob.bytes.size(), &s->arena);
     if (rc) { delete s; return rc; }
     cx.live.push_back(s);
@@ -445,6 +477,7 @@ int upload_scene(Context& cx, const rt_scene_desc* d, rt_scene** out) {
     h.runs = (const int4*)(base + o_runs); h.clusters = (const float4*)(base + o_clusters); h.obj_orig = (const int*)(base + o_obj_orig);
     h.n_clusters = (int)s->clusters.size();
     h.masks = (const float4*)(base + o_masks); h.mask_scale = s->mask_scale;
+    h.grid = s->grid; h.grid_masks = (const uint32_t*)(base + o_grid_masks);
     s->width = d->width; s->height = d->height;
     h.n_leaves = d->n_leaves; h.n_ops = d->n_ops;
     h.off_obj_meta = s->clustered ? 0 : d->n_objects;                // scenes with clustered runs read top-level geometry / meta from global memory
@@ -455,6 +488,9 @@ int upload_scene(Context& cx, const rt_scene_desc* d, rt_scene** out) {
     h.off_masks = h.off_clusters + h.n_clusters;
     h.off_ops_bytes = 16 * (h.off_masks + (int)s->masks.size());
     h.smem_bytes = h.off_ops_bytes + 4 * d->n_ops;
+    h.n_grid_cells = (int)(s->grid_masks.size() / rtd::kGridMaxWords);
+    h.off_grid_bytes = (h.smem_bytes + 15) & ~15;
+    if (h.n_grid_cells) h.smem_bytes = h.off_grid_bytes + 16 * h.n_grid_cells;
     s->fits_const = (size_t)h.smem_bytes <= kSceneSmemBudget;
     // Wavefront kernel only where most surfaces spawn secondary rays: its per-sample state traffic costs ~10 % on scenes
     // whose ray trees are mostly depth 1 (snorlax with one reflective sphere), and gains ~6 % on the all-glass lattice.
@@ -743,7 +779,7 @@ int rt_debug_set_option(const char* name, int value) {
     std::lock_guard<std::mutex> lk(g_mu);
     const std::string n(name);
     std::atomic<int>* slot = n == "flat" ? &g_opts.flat : n == "cull" ? &g_opts.cull : n == "wavefront" ? &g_opts.wavefront
-              : n == "global_scene" ? &g_opts.global_scene : n == "mt_sequential" ? &g_opts.mt_sequential : nullptr;
+              : n == "global_scene" ? &g_opts.global_scene : n == "mt_sequential" ? &g_opts.mt_sequential : n == "grid" ? &g_opts.grid : nullptr;
     if (!slot) return fail(RT_ERR_ARG, "rt_debug_set_option: unknown option " + n);
     slot->store(value < 0 ? -1 : (value ? 1 : 0));
     return RT_OK;

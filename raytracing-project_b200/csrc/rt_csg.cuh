@@ -64,7 +64,7 @@ RT_CSG_COLD Ivl csg_sweep(int op, Ivl A, Ivl B) {
     // finite ends only (csg.cpp:76-81), initial order A-enter, A-exit, B-enter, B-exit
     {
         const float ts[4] = {A.t0, A.t1, B.t0, B.t1};
-        const bool ok[4] = {A.ok, A.ok, B.ok, B.ok};
+        const bool ok[4] = {A.ok != 0, A.ok != 0, B.ok != 0, B.ok != 0};
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             bool use = ok[i] && isfinite(ts[i]);

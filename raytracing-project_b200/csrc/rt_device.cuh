@@ -16,6 +16,7 @@
 
 #include "../../include/rt_b200.h"
 #include "rt_cull.cuh"
+#include "rt_grid.cuh"
 
 namespace rtd {
 
@@ -46,6 +47,10 @@ struct SceneHeader {
     const uint32_t* cull_plane_bits;                  // one bit per entry: the entry is a half-space surface
     int cull_words, cull_leaf_word;                   // words per bundle (0: scene not culled), first word of the leaf section
     int off_cand_bytes;                               // CandShared + masks in dynamic shared memory
+    // uniform grid over the plain spheres / pokeballs (rt_grid.cuh): scenes scanned by incoherent rays; grid.words == 0: none
+    GridHeader grid;
+    const uint32_t* grid_masks;                       // 4 candidate words per cell (+ the ALWAYS cell), bit i = device object i
+    int off_grid_bytes, n_grid_cells;                 // staged copy: byte offset in the shared-memory image; cells incl. the ALWAYS cell
 };
 
 enum { RUN_SPHERE = 0, RUN_HALFSPACE = 1, RUN_POKEBALL = 2, RUN_GENERIC = 3 };
@@ -86,6 +91,11 @@ template <bool C> struct SV {
     static __device__ __forceinline__ float4 fallback(int i)  { return __ldg(c_hdr.fallbacks + i); }
     static __device__ __forceinline__ float4 cluster(int i)   { return C ? reinterpret_cast<const float4*>(s_scene)[c_hdr.off_clusters + i] : __ldg(c_hdr.clusters + i); }
     static __device__ __forceinline__ int    obj_orig(int i)  { return __ldg(c_hdr.obj_orig + i); }
+    // the four candidate words of grid cell i (rt_grid.cuh): staged behind the CSG ops when the scene is staged
+    static __device__ __forceinline__ GridWords grid_cell(int i) {
+        const uint4 v = C ? reinterpret_cast<const uint4*>(s_scene + c_hdr.off_grid_bytes)[i] : __ldg(reinterpret_cast<const uint4*>(c_hdr.grid_masks) + i);
+        GridWords g; g.x = v.x; g.y = v.y; g.z = v.z; g.w = v.w; return g;
+    }
     // base pointers for sphere_mask (the mask table mirrors obj_geom | leaf_geom | clusters)
     static __device__ __forceinline__ const float4* mask_ptr(int i)    { return C ? reinterpret_cast<const float4*>(s_scene) + c_hdr.off_masks + i : c_hdr.masks + i; }
 #if RT_MASK_EXACT
@@ -118,6 +128,8 @@ template <bool C> __device__ __forceinline__ void stage_scene() {
     for (int i = t; i < n_masks; i += n) dst[c_hdr.off_masks + i] = __ldg(c_hdr.masks + i);
     uint32_t* ops = reinterpret_cast<uint32_t*>(s_scene + c_hdr.off_ops_bytes);
     for (int i = t; i < c_hdr.n_ops; i += n) ops[i] = __ldg(c_hdr.ops + i);
+    uint4* gc = reinterpret_cast<uint4*>(s_scene + c_hdr.off_grid_bytes);
+    for (int i = t; i < c_hdr.n_grid_cells; i += n) gc[i] = __ldg(reinterpret_cast<const uint4*>(c_hdr.grid_masks) + i);
     __syncthreads();
 }
 // materials are indexed per lane (divergent) -> always the global read-only path

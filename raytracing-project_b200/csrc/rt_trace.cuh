@@ -74,11 +74,50 @@ struct ScanResult { int best; float t; uint32_t code; float tent; };
 
 // (1) A ray of a round's bundle (camera rays, their shadow rays): the candidates are the set bits of the round's mask
 // `cand` (rt_device.cuh cand_build) — objects in device order, then the CSG leaves.  A handful of bits per query.
+#ifndef RT_SCAN_TWO_PHASE
+#define RT_SCAN_TWO_PHASE 0          // A/B: plain primitives of a word first (classified by bit planes, no meta load, no call in the loop), generic objects after
+#endif
 template <bool C, bool K>
 __device__ __forceinline__ void scan_masked(V3 o, V3 d, float tmin, float tmax, const bool any, const int cb, ScanResult& res, unsigned& tests) {
     int best = -1; float best_t = tmax; uint32_t best_code = 0; float best_tent = 0.f;
     const int W = c_hdr.cull_leaf_word;
     const uint32_t* cand = cand_words(cb);
+#if RT_SCAN_TWO_PHASE
+    // Per word: the plain spheres / pokeballs / half-spaces first — classified by two bit planes of the culling table, no
+    // meta record is loaded and the loop contains no call — then the generic objects.  The order inside a word changes, the
+    // result does not: plain primitives accept t <= best_t (the later index wins an exact tie, as in scene.cpp:15-21) and
+    // are still visited in index order; a generic object visited after a plain one of higher index must not take over an
+    // exact tie (CSG programs and wrapped primitives use t < tmax and never do, transform.cpp:38 / csg.cpp:176).
+    if (!K) {
+        const int Wc = c_hdr.cull_words;
+        for (int w = 0; w < W; ++w) {
+            const uint32_t bits = cand[w];
+            if (!bits) continue;
+            const uint32_t hs = __ldg(c_hdr.cull_plane_bits + Wc + w), gen = __ldg(c_hdr.cull_plane_bits + 2 * Wc + w);
+            uint32_t pb = bits & ~gen;
+            while (pb) {
+                const int k = __ffs(pb) - 1; pb &= pb - 1;
+                const int i = (w << 5) + k;
+                ++tests;
+                const float4 g = SV<C>::template obj_geom_k<K>(i);
+                float t;
+                if (!(((hs >> k) & 1u) ? plane_t(g, o, d, tmin, best_t, t) : sphere_t(g, o, d, tmin, best_t, t))) continue;
+                best = i; best_t = t;
+                if (any) goto done;
+            }
+            uint32_t gb = bits & gen;
+            while (gb) {
+                const int i = (w << 5) + __ffs(gb) - 1; gb &= gb - 1;
+                float t, tent; uint32_t code;
+                if (!generic_hit<C, K>(i, o, d, tmin, best_t, cb, t, code, tent, tests)) continue;
+                if (t == best_t && i < best) continue;                       // (an exact tie stays with the later index)
+                best = i; best_t = t; best_code = code; best_tent = tent;
+                if (any) goto done;
+            }
+        }
+        goto done;
+    }
+#endif
     for (int w = 0; w < W; ++w) {
         uint32_t bits = cand[w];
         while (bits) {
@@ -113,6 +152,16 @@ template <bool C, bool K>
 __device__ __forceinline__ void scan_body(V3 o, V3 d, float tmin, float tmax, const bool any, ScanResult& res, unsigned& tests) {
     int best = -1; float best_t = tmax; uint32_t best_code = 0; float best_tent = 0.f;
     const int n_runs = c_hdr.n_runs;
+    // Scenes with a grid (rt_grid.cuh): the candidates of every unclustered run of plain spheres / pokeballs
+    // come from ONE walk through the cells the ray crosses instead of one conservative test per sphere and run.
+    GridWords gw = {0u, 0u, 0u, 0u};
+    bool grid = false;
+    if (c_hdr.grid.words) {
+        const float oo[3] = {o.x, o.y, o.z}, dd[3] = {d.x, d.y, d.z};
+        const int visited = grid_walk(c_hdr.grid, [](int c) { return SV<C>::grid_cell(c); }, oo, dd, tmin, tmax, gw);
+        grid = visited >= 0;                                                 // (NaN in the ray: the per-sphere masks decide)
+        tests += (unsigned)max(visited, 0);
+    }
     for (int rr = 0; rr < n_runs; ++rr) {
         const int4 run = SV<C>::run((any && !K) ? n_runs - 1 - rr : rr);
         const int first = run.y, end = run.y + run.z;
@@ -146,8 +195,17 @@ __device__ __forceinline__ void scan_body(V3 o, V3 d, float tmin, float tmax, co
         } else if (run.x == RUN_SPHERE || run.x == RUN_POKEBALL) {
             for (int c0 = first; c0 < end; c0 += 32) {                       // candidates first, finished in JSON order
                 const int n = min(32, end - c0);
-                tests += n;
-                uint32_t mask = sphere_mask<C>(SV<C>::obj_ptr(c0), n, o, d);
+                uint32_t mask;
+                if (grid) {                                                  // bits [c0, c0 + n) of the walk's words
+                    const int w = c0 >> 5, sh = c0 & 31;
+                    const uint32_t lo = w == 0 ? gw.x : w == 1 ? gw.y : w == 2 ? gw.z : gw.w;
+                    const uint32_t hi = (sh + n > 32) ? (w == 0 ? gw.y : w == 1 ? gw.z : w == 2 ? gw.w : 0u) : 0u;
+                    mask = __funnelshift_r(lo, hi, sh) & (n >= 32 ? 0xffffffffu : ((1u << n) - 1u));
+                    tests += __popc(mask);
+                } else {
+                    tests += n;
+                    mask = sphere_mask<C>(SV<C>::obj_ptr(c0), n, o, d);
+                }
                 while (mask) {
                     const int i = c0 + __ffs(mask) - 1; mask &= mask - 1;
                     float t;

@@ -214,6 +214,29 @@ def test_culling_does_not_change_a_bit(gpu, name, force):
         print(f"{name}/{mode}: primitive tests {out[0, mode, 'stats']['prim_tests']} -> {out[1, mode, 'stats']['prim_tests']}")
 
 
+@pytest.mark.parametrize("name", ["synthetic_b_small", "big_floor", "penguin_small", "pokeballs_small", "quirks"])
+def test_grid_does_not_change_a_bit(gpu, name, force):
+    """Uniform grid for rays that belong to no bundle (csrc/rt_grid.cuh; the library builds it for bounce-heavy scenes with
+    at least 24 plain spheres) against the per-sphere conservative scans: frame, ids and ray counts identical with either
+    kernel, and the walk must save primitive tests where a grid was built."""
+    out = {}
+    for wave in (0, 1):
+        for grid in (0, 1):
+            force("wavefront", wave); force("grid", grid)
+            sc = gpu.load_scene_from_json(scene_path(name))
+            out[wave, grid], tr = render_gpu(gpu, sc, "standard")
+            out[wave, grid, "stats"] = dict(tr.last_stats)
+            sc.close()
+    for key in ((0, 1), (1, 0), (1, 1)):
+        for k in ("rgb8", "fb", "ids"):
+            assert np.array_equal(out[0, 0][k], out[key][k]), (key, k)
+        for k in ("primary_rays", "shadow_rays", "secondary_rays"):
+            assert out[0, 0, "stats"][k] == out[key + ("stats",)][k], (key, k)
+    print(f"{name}: primitive tests {out[1, 0, 'stats']['prim_tests']} -> {out[1, 1, 'stats']['prim_tests']} with the grid")
+    if name in ("synthetic_b_small", "big_floor"):         # (the other scenes have fewer than 24 plain spheres: no grid)
+        assert 2 * out[1, 1, "stats"]["prim_tests"] < out[1, 0, "stats"]["prim_tests"]
+
+
 def test_every_scene_data_path_agrees(gpu, force):
     """global_scene hook: the scene read through the global read-only path instead of the staged shared-memory image."""
     ref = None
