@@ -321,7 +321,7 @@ def mt_jump_host(seed: int, log2_twists: int) -> np.ndarray:
     return out
 
 
-DEBUG_OPTIONS = ("flat", "cull", "wavefront", "global_scene", "mt_sequential", "grid")
+DEBUG_OPTIONS = ("flat", "cull", "wavefront", "global_scene", "mt_sequential", "grid", "grid_cells")
 
 
 def debug_option(name: str, value: int = -1) -> None:

@@ -70,7 +70,7 @@ Context* g_ctxs[kMaxDevices] = {};        // created on demand (rt_init, rt_init
 Context* g_cur = nullptr;                 // the process's render device (rt_init)
 std::mutex g_mu;                          // guards g_ctxs / g_cur / the host-frame registry; taken BEFORE a context's mutex, never after
 // Test hooks (rt_debug_set_option): -1 = the library's own choice, 0 / 1 = forced.  Never read from the environment.
-struct DebugOptions { std::atomic<int> flat{-1}, cull{-1}, wavefront{-1}, global_scene{-1}, mt_sequential{-1}, grid{-1}; };
+struct DebugOptions { std::atomic<int> flat{-1}, cull{-1}, wavefront{-1}, global_scene{-1}, mt_sequential{-1}, grid{-1}, grid_cells{-1}; };
 DebugOptions g_opts;                      // (atomics: read under a context's mutex, written under g_mu)
 constexpr size_t kSceneSmemBudget = 80 * 1024;   // + 25 KB of MT19937 buffers: two CTAs per SM still fit in 227 KB
 
@@ -146,7 +146,7 @@ float4 bound_of(const rt_prim* objs, const int* idx, int n) {
     return make_float4((float)c[0], (float)c[1], (float)c[2], (float)(R * 1.002 + 1e-3));
 }
 
-void build_host_arrays(const rt_scene_desc& d, rt_scene& s, bool want_grid = false) {
+void build_host_arrays(const rt_scene_desc& d, rt_scene& s, bool want_grid = false, double grid_cells_per_sphere = 2.0) {
     // device order of the top-level objects: JSON order, except inside clustered runs (see above)
     std::vector<int> order(d.n_objects);
     for (int i = 0; i < d.n_objects; ++i) order[i] = i;
@@ -262,7 +262,7 @@ void build_host_arrays(const rt_scene_desc& d, rt_scene& s, bool want_grid = fal
                 bit.push_back((int)i);
             }
         }
-        if ((int)bit.size() >= kGridMinSpheres) rtd::grid_build(sph.data(), bit.data(), (int)bit.size(), d.n_objects, s.grid, s.grid_masks);
+        if ((int)bit.size() >= kGridMinSpheres) rtd::grid_build(sph.data(), bit.data(), (int)bit.size(), d.n_objects, s.grid, s.grid_masks, grid_cells_per_sphere);
     }
     // Mask table of sphere_mask: (c, |c|^2 - r^2 - 2^-16 (|c|^2 + r^2)) for every entry of obj_geom | leaf_geom | clusters
     // (entries that are not sphere-like are never scanned through it): the primitive's own share of the scan's rounding
@@ -448,7 +448,7 @@ int upload_scene(Context& cx, const rt_scene_desc* d, rt_scene** out) {
     bool want_grid = d->recursion >= 2 && d->n_materials > 0 && 2 * n_bounce0 >= d->n_materials;
     if (g_opts.wavefront.load() >= 0) want_grid = g_opts.wavefront.load() == 1;
     if (g_opts.grid.load() >= 0) want_grid = g_opts.grid.load() == 1;       // test hook
-    build_host_arrays(*d, *s, want_grid);
+    build_host_arrays(*d, *s, want_grid, g_opts.grid_cells.load() > 0 ? (double)g_opts.grid_cells.load() : 2.0);     // measured on synthetic-B 1K: 1 / 2 / 4 / 8 / 16 / 32 cells per sphere = 29.7 / 28.5 / 29.5 / 29.8 / 34.5 / 41.4 ms (no grid: 31.7)
     Blob blob;
     const size_t o_obj_geom = blob.add(s->obj_geom), o_obj_meta = blob.add(s->obj_meta), o_leaf_geom = blob.add(s->leaf_geom),
                  o_leaf_meta = blob.add(s->leaf_meta), o_pokeballs = blob.add(s->pokeballs), o_affines = blob.add(s->affines),
@@ -779,9 +779,9 @@ int rt_debug_set_option(const char* name, int value) {
     std::lock_guard<std::mutex> lk(g_mu);
     const std::string n(name);
     std::atomic<int>* slot = n == "flat" ? &g_opts.flat : n == "cull" ? &g_opts.cull : n == "wavefront" ? &g_opts.wavefront
-              : n == "global_scene" ? &g_opts.global_scene : n == "mt_sequential" ? &g_opts.mt_sequential : n == "grid" ? &g_opts.grid : nullptr;
+              : n == "global_scene" ? &g_opts.global_scene : n == "mt_sequential" ? &g_opts.mt_sequential : n == "grid" ? &g_opts.grid : n == "grid_cells" ? &g_opts.grid_cells : nullptr;
     if (!slot) return fail(RT_ERR_ARG, "rt_debug_set_option: unknown option " + n);
-    slot->store(value < 0 ? -1 : (value ? 1 : 0));
+    slot->store(value < 0 ? -1 : (slot == &g_opts.grid_cells ? value : (value ? 1 : 0)));      // grid_cells: cells per sphere
     return RT_OK;
 }
 

@@ -105,7 +105,7 @@ RT_GRID_FN int grid_walk(const GridHeader& g, CellLoad cell, const float o[3], c
 namespace rtd {
 // Host: build the grid over `n` spheres (cx, cy, cz, r) whose candidate bits are `bit[i]` (device object index).  Returns
 // false (no grid) when there is nothing finite to bin.  target_cells ~ cells per sphere.
-inline bool grid_build(const float* spheres4, const int* bit, int n, int n_bits, GridHeader& g, std::vector<uint32_t>& masks, double cells_per_sphere = 8.0) {
+inline bool grid_build(const float* spheres4, const int* bit, int n, int n_bits, GridHeader& g, std::vector<uint32_t>& masks, double cells_per_sphere = 2.0) {
     g = GridHeader{};
     if (n <= 0 || n_bits > 32 * kGridMaxWords) return false;
     // spheres beyond 8 x the median radius are not binned (ALWAYS mask)

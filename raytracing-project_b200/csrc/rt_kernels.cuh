@@ -456,10 +456,10 @@ __global__ void __launch_bounds__(kRenderThreads, RT_WAVE_BLOCKS) render_wavefro
                 RGBf c = rgb(0.f, 0.f, 0.f);
                 Hit ph; bool phit = false;
                 if (limit <= 0) {                                    // tracer.cpp:26: black, but the id buffer is still defined
-                    if (valid) { ++cnt.primary; if (prm.ids) phit = closest_hit<C, K, false>(o, d, 1e-4f, kInf, -1, ph, cnt); }
+                    if (valid) { ++cnt.primary; if (prm.ids) phit = closest_hit<C, K, false, true>(o, d, 1e-4f, kInf, -1, ph, cnt); }
                 } else {
                     const int cand0 = camera_pass ? camera_mask(valid, d, cnt) : -1;
-                    more = !ray_step<C, K, M, false>(valid, camera_pass, cand0, o, d, depth, sp + 2, c, ph, phit, cnt) && valid;
+                    more = !ray_step<C, K, M, false, true>(valid, camera_pass, cand0, o, d, depth, sp + 2, c, ph, phit, cnt) && valid;
                 }
                 if (valid) {
                     if (primary && prm.ids) {

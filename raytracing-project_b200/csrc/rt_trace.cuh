@@ -148,7 +148,8 @@ done:
 // the candidates of a run from the per-lane conservative mask (sphere_mask).  Scenes of a few dozen primitives walk the
 // runs backwards for any-hit (the order cannot be observed, scene.cpp:33-42 returns a bool, and later objects are usually
 // the foreground detail that casts the shadows).
-template <bool C, bool K>
+// G: the kernel serves scenes with a grid (rt_grid.cuh; the wavefront kernel only: the other kernels carry none of that code)
+template <bool C, bool K, bool G = false>
 __device__ __forceinline__ void scan_body(V3 o, V3 d, float tmin, float tmax, const bool any, ScanResult& res, unsigned& tests) {
     int best = -1; float best_t = tmax; uint32_t best_code = 0; float best_tent = 0.f;
     const int n_runs = c_hdr.n_runs;
@@ -156,7 +157,7 @@ __device__ __forceinline__ void scan_body(V3 o, V3 d, float tmin, float tmax, co
     // come from ONE walk through the cells the ray crosses instead of one conservative test per sphere and run.
     GridWords gw = {0u, 0u, 0u, 0u};
     bool grid = false;
-    if (c_hdr.grid.words) {
+    if (G && c_hdr.grid.words) {
         const float oo[3] = {o.x, o.y, o.z}, dd[3] = {d.x, d.y, d.z};
         const int visited = grid_walk(c_hdr.grid, [](int c) { return SV<C>::grid_cell(c); }, oo, dd, tmin, tmax, gw);
         grid = visited >= 0;                                                 // (NaN in the ray: the per-sphere masks decide)
@@ -196,7 +197,7 @@ __device__ __forceinline__ void scan_body(V3 o, V3 d, float tmin, float tmax, co
             for (int c0 = first; c0 < end; c0 += 32) {                       // candidates first, finished in JSON order
                 const int n = min(32, end - c0);
                 uint32_t mask;
-                if (grid) {                                                  // bits [c0, c0 + n) of the walk's words
+                if (G && grid) {                                             // bits [c0, c0 + n) of the walk's words
                     const int w = c0 >> 5, sh = c0 & 31;
                     const uint32_t lo = w == 0 ? gw.x : w == 1 ? gw.y : w == 2 ? gw.z : gw.w;
                     const uint32_t hi = (sh + n > 32) ? (w == 0 ? gw.y : w == 1 ? gw.z : w == 2 ? gw.w : 0u) : 0u;
@@ -246,10 +247,10 @@ done:
 // cost them more than it saved).  The test count is returned by value (a reference would pin the caller's counter to
 // local memory).
 struct ScanOut { ScanResult r; unsigned tests; };
-template <bool C, bool K>
+template <bool C, bool K, bool G = false>
 __device__ __noinline__ ScanOut scan_shared(V3 o, V3 d, float tmin, float tmax, bool any) {
     ScanOut out; out.tests = 0;
-    scan_body<C, K>(o, d, tmin, tmax, any, out.r, out.tests);
+    scan_body<C, K, G>(o, d, tmin, tmax, any, out.r, out.tests);
     return out;
 }
 #ifndef RT_SCAN_SHARED
@@ -267,20 +268,20 @@ __device__ __noinline__ ScanOut scan_masked_shared(V3 o, V3 d, float tmin, float
     return out;
 }
 // M: the kernel was built with round-level masks (rt_device.cuh); kernels without them contain none of that code.
-template <bool C, bool K, bool M, bool ANY>
+template <bool C, bool K, bool M, bool ANY, bool G = false>
 __device__ __forceinline__ void scan(V3 o, V3 d, float tmin, float tmax, const int cb, ScanResult& res, Counters& cnt) {
     if (M && cb >= 0) {
         if (RT_MASKED_CALL) { const ScanOut so = scan_masked_shared<C, K>(o, d, tmin, tmax, ANY, cb); res = so.r; cnt.tests += so.tests; }
         else scan_masked<C, K>(o, d, tmin, tmax, ANY, cb, res, cnt.tests);
     }
-    else if (K || RT_SCAN_SHARED) { const ScanOut so = scan_shared<C, K>(o, d, tmin, tmax, ANY); res = so.r; cnt.tests += so.tests; }
-    else scan_body<C, K>(o, d, tmin, tmax, ANY, res, cnt.tests);
+    else if (K || RT_SCAN_SHARED) { const ScanOut so = scan_shared<C, K, G>(o, d, tmin, tmax, ANY); res = so.r; cnt.tests += so.tests; }
+    else scan_body<C, K, G>(o, d, tmin, tmax, ANY, res, cnt.tests);
 }
 
-template <bool C, bool K, bool M>
+template <bool C, bool K, bool M, bool G = false>
 __device__ __forceinline__ bool closest_hit(V3 o, V3 d, float tmin, float tmax, const int cb, Hit& hit, Counters& cnt) {
     ScanResult sr;
-    scan<C, K, M, false>(o, d, tmin, tmax, cb, sr, cnt);
+    scan<C, K, M, false, G>(o, d, tmin, tmax, cb, sr, cnt);
     const int best = sr.best;
     if (best < 0) return false;
     // ---- finalise the winner: normal, front_face, material, id code ----
@@ -320,10 +321,10 @@ __device__ __forceinline__ bool closest_hit(V3 o, V3 d, float tmin, float tmax, 
     return true;
 }
 
-template <bool C, bool K, bool M>
+template <bool C, bool K, bool M, bool G = false>
 __device__ __forceinline__ bool occluded(V3 o, V3 d, float tmin, float tmax, const int cb, Counters& cnt) {
     ScanResult sr;
-    scan<C, K, M, true>(o, d, tmin, tmax, cb, sr, cnt);
+    scan<C, K, M, true, G>(o, d, tmin, tmax, cb, sr, cnt);
     return sr.best >= 0;
 }
 
@@ -393,7 +394,7 @@ __device__ __forceinline__ void light_shade(int l, const float4 m0, float ks, fl
 //               bundle towards that light, one entry per lane, into its own mask words — no barrier, no shared atomics, and
 //               the warps of a CTA need not walk in step.
 enum { kListsNone = 0, kListsCta = 1, kListsWarp = 2 };
-template <bool C, bool K, bool M>
+template <bool C, bool K, bool M, bool G = false>
 __device__ __forceinline__ RGBf shade(bool lit, const int LISTS, const Hit& h, V3 p, V3 wo, Counters& cnt) {
     const float eps = fmaxf(1e-3f, 1e-4f * h.t);                             // shading.cpp:43
     const V3 so = madd(p, h.n, eps);
@@ -458,7 +459,7 @@ __device__ __forceinline__ RGBf shade(bool lit, const int LISTS, const Hit& h, V
             }
             if (need) {
                 ++cnt.shadow;
-                if (!occluded<C, K, M>(so, normalized(wi), eps, tmaxS, cb, cnt)) vis |= 1u << (l & 31);   // Ray ctor re-normalises (core.h:278)
+                if (!occluded<C, K, M, G>(so, normalized(wi), eps, tmaxS, cb, cnt)) vis |= 1u << (l & 31);   // Ray ctor re-normalises (core.h:278)
             }
             if (lists == kListsWarp) __syncwarp();                          // the words are rewritten for the next light
         }
@@ -487,21 +488,21 @@ __device__ __forceinline__ RGBf shade(bool lit, const int LISTS, const Hit& h, V
 // (o, d, sp) is its next ray.  FLAT: no ray of the scene can spawn a child (no reflective / refractive material, or
 // recursion == 1): no frames are touched and every tree finishes with its first ray.  LISTS: the ray is a camera ray of
 // a round — `cand` is the round's mask of the camera bundle, ALL threads of the CTA make the call (see shade).
-template <bool C, bool K, bool M, bool FLAT>
+template <bool C, bool K, bool M, bool FLAT, bool G = false>
 __device__ __forceinline__ bool ray_step(bool alive, const int LISTS, const int cb, V3& o, V3& d, int& sp, float4* __restrict__ frames,
                                          RGBf& result, Hit& primary, bool& primary_hit, Counters& cnt) {
     const int limit = c_hdr.recursion;
     Hit h; h.mat = -1; h.t = 0.f; h.n = mk(0.f, 1.f, 0.f); h.front = true; h.code = -1;
     bool hit = false;
     if (alive) {
-        hit = closest_hit<C, K, M>(o, d, 1e-4f, kInf, cb, h, cnt);         // tracer.cpp:29
+        hit = closest_hit<C, K, M, G>(o, d, 1e-4f, kInf, cb, h, cnt);      // tracer.cpp:29
         if (FLAT || LISTS || sp == 0) { ++cnt.primary; primary = h; primary_hit = hit; } else ++cnt.secondary;
     }
     const V3 p = madd(o, d, h.t);
     const V3 wo = normalized(neg(d));
     const bool lit = hit && h.mat >= 0;
     if (!LISTS && !alive) return true;
-    const RGBf total = shade<C, K, M>(lit, LISTS, h, p, wo, cnt);           // tracer.cpp:31
+    const RGBf total = shade<C, K, M, G>(lit, LISTS, h, p, wo, cnt);        // tracer.cpp:31
     if (!alive) return true;
     if (!hit) result = rgb(c_hdr.bg[0], c_hdr.bg[1], c_hdr.bg[2]);          // tracer.cpp:72
     else if (!lit) result = rgb(1.f, 0.f, 1.f);                              // shading.cpp:33

@@ -11,6 +11,8 @@ for kv in os.environ.get("RT_OPT", "").split(","):      # e.g. RT_OPT=cull=0,fla
     if "=" in kv:
         rt.debug_option(kv.split("=")[0], int(kv.split("=")[1]))
 tr = rt.Tracer(rt.load_scene_from_json(path), mode)
+import zlib
 for _ in range(n):
-    tr.render(want_rgb8=True)
-    print(tr.last_stats)
+    out = tr.render(want_rgb8=True)
+    st = dict(tr.last_stats); st["rgb8_crc32"] = zlib.crc32(out["rgb8"].tobytes())      # frame identity across variants
+    print(st)
