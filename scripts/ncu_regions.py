@@ -3,18 +3,20 @@
 moves, local-memory traffic and control flow inside each region.  Input: ncu --page source --print-source cuda,sass --csv.
 Usage: ncu_regions.py src.csv"""
 import csv, re, sys, collections
-REGIONS = [
-    ("tile prologue: MT19937 twists, checkpoint load", [("rt_kernels.cuh", 229, 245), ("mt19937.cuh", 1, 999), ("rt_kernels.cuh", 184, 205)]),
-    ("round: sample set-up, jitter, camera ray (FP64)", [("rt_kernels.cuh", 260, 291), ("rt_kernels.cuh", 114, 128)]),
-    ("round: resolve + store", [("rt_kernels.cuh", 292, 312), ("rt_kernels.cuh", 130, 160)]),
-    ("round masks: box reduce + cand_build + bundle tests", [("rt_device.cuh", 165, 295), ("rt_cull.cuh", 1, 999), ("rt_kernels.cuh", 162, 172), ("device_atomic_functions.hpp", 1, 9999)]),
-    ("scan loop (masked / run-based) + scan glue", [("rt_trace.cuh", 68, 207)]),
-    ("sphere_t / plane_t / sphere_disc / sphere_mask", [("rt_device.cuh", 297, 399)]),
-    ("generic_hit + run_program + leaf_interval + csg", [("rt_trace.cuh", 15, 67), ("rt_device.cuh", 400, 582), ("rt_csg.cuh", 1, 999)]),
-    ("closest_hit finalise (normal, material, code)", [("rt_trace.cuh", 208, 257)]),
-    ("shade loop + light_vector + light_shade", [("rt_trace.cuh", 258, 390)]),
-    ("ray_step / trace (recursion glue)", [("rt_trace.cuh", 391, 510)]),
-    ("vector helpers (dot, madd, normalized, SV accessors)", [("rt_device.cuh", 60, 164)]),
+REGIONS = [   # line ranges of the round-2 final sources (rt_kernels.cuh 729, rt_trace.cuh 597, rt_device.cuh 632 lines)
+    ("tile prologue: MT19937 twists, checkpoint load, tile mask box", [("rt_kernels.cuh", 229, 252), ("mt19937.cuh", 1, 999), ("rt_kernels.cuh", 184, 211)]),
+    ("round: sample set-up, jitter, camera ray (FP64)", [("rt_kernels.cuh", 253, 297), ("rt_kernels.cuh", 114, 128)]),
+    ("round: resolve + store", [("rt_kernels.cuh", 298, 320), ("rt_kernels.cuh", 130, 160)]),
+    ("round masks: box reduce + cand_build + bundle tests", [("rt_device.cuh", 185, 323), ("rt_cull.cuh", 1, 999), ("rt_kernels.cuh", 162, 172), ("device_atomic_functions.hpp", 1, 9999)]),
+    ("scan loops (masked / run-based) + scan glue", [("rt_trace.cuh", 68, 280)]),
+    ("grid walk (rt_grid.cuh)", [("rt_grid.cuh", 1, 999)]),
+    ("sphere_t / plane_t / sphere_disc / sphere_mask", [("rt_device.cuh", 324, 427)]),
+    ("generic_hit + run_program + leaf_interval + csg", [("rt_trace.cuh", 15, 67), ("rt_device.cuh", 428, 632), ("rt_csg.cuh", 1, 999)]),
+    ("closest_hit finalise (normal, material, code)", [("rt_trace.cuh", 281, 330)]),
+    ("shade loop + light_vector + light_shade", [("rt_trace.cuh", 331, 478)]),
+    ("ray_step / trace (recursion glue)", [("rt_trace.cuh", 479, 597)]),
+    ("wavefront kernel body (queue, state)", [("rt_kernels.cuh", 321, 528)]),
+    ("vector helpers (dot, madd, normalized, SV accessors)", [("rt_device.cuh", 60, 184)]),
 ]
 CLASS = {"fp32": {"FFMA", "FMUL", "FADD", "FSETP", "FSEL", "FMNMX", "FMNMX3", "MUFU", "FCHK", "FFMA2", "FMUL2", "FADD2"},
          "fp64": {"DFMA", "DMUL", "DADD", "DSETP", "F2F", "I2F", "F2I", "DMNMX"},
