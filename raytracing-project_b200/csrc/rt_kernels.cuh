@@ -241,6 +241,10 @@ __global__ void __launch_bounds__(kRenderThreads, (!F && !K) ? RT_NONFLAT_BLOCKS
         // --- the tile's 4992 raw outputs: checkpoint + 8 twists (one barrier each) ---
         for (int k = tid; k < mt::kN; k += kRenderThreads) raw[k] = __ldg(prm.mt_table + (long long)local * mt::kN + k);
         const long long pix0 = tile * mt::kPixelsPerTile;
+        // row and column of the tile's first pixel: ONE 64-bit division per thread and tile; a sample's pixel follows by
+        // additions (a 64-bit division per sample was 60 instructions of its ~3 700)
+        const long long tile_y0 = pix0 / nx;
+        const int tile_x0 = (int)(pix0 - tile_y0 * nx);
         if (M && RT_TILE_CAMERA_MASK && tid == kRenderThreads - 1) tile_direction_box(pix0, (int)min((long long)mt::kPixelsPerTile, prm.n_pixels - pix0), nx, ny);
         __syncthreads();
 #pragma unroll 1
@@ -282,7 +286,9 @@ __global__ void __launch_bounds__(kRenderThreads, (!F && !K) ? RT_NONFLAT_BLOCKS
             int x = 0, yy = 0;
             V3 o = mk(0.f, 0.f, 0.f), d = mk(0.f, 1.f, 0.f);
             if (active) {
-                const int y = (int)(p / nx); x = (int)(p - (long long)y * nx); yy = ny - 1 - y;   // row flip on store (tracer.cpp:297)
+                int y = (int)tile_y0; x = tile_x0 + (j >> 3);
+                while (x >= nx) { x -= nx; ++y; }                            // (a tile spans two rows at most unless the frame is narrower than 156 pixels)
+                yy = ny - 1 - y;                                              // row flip on store (tracer.cpp:297)
                 uint4 w = *reinterpret_cast<const uint4*>(raw + mt::kN + 4 * j);
                 w.x = mt::temper(w.x); w.y = mt::temper(w.y); w.z = mt::temper(w.z); w.w = mt::temper(w.w);
                 const double jx = mt::jitter(w.x, w.y), jy = mt::jitter(w.z, w.w);              // dx first (tracer.cpp:293)
@@ -574,7 +580,8 @@ __global__ void __launch_bounds__(256, RT_PAPER_BLOCKS) paper_gbuffer_kernel(GBu
     stage_scene<C>();
     // pixels past the end and rows this rank does not need keep the CTA company at the barriers of the round
     const bool inside = q < (long long)nx * ny;
-    const int y = inside ? (int)(q / nx) : 0, x = inside ? (int)(q - (long long)y * nx) : 0;
+    const bool small = (long long)nx * ny <= 0xffffffffLL;                  // 32-bit division wherever the pixel index fits
+    const int y = !inside ? 0 : small ? (int)((unsigned)q / (unsigned)nx) : (int)(q / nx), x = inside ? (int)(q - (long long)y * nx) : 0;
     const bool own = inside && paper_row_owned(y, rank, world);
     const bool need = inside && (own || (y > 0 && paper_row_owned(y - 1, rank, world)) || (y + 1 < ny && paper_row_owned(y + 1, rank, world)));
     // Camera::generate_ray (camera.h:44-58): pixel centre, j flipped
@@ -606,7 +613,7 @@ __global__ void __launch_bounds__(256) paper_post_kernel(GBuf gb, uchar4* rgba8,
     __shared__ int s_any;
     const long long q0 = (long long)blockIdx.x * blockDim.x, q = q0 + threadIdx.x;
     const long long npx = (long long)nx * ny;
-    const int y = q < npx ? (int)(q / nx) : 0, x = q < npx ? (int)(q - (long long)y * nx) : 0;
+    const int y = q >= npx ? 0 : npx <= 0xffffffffLL ? (int)((unsigned)q / (unsigned)nx) : (int)(q / nx), x = q < npx ? (int)(q - (long long)y * nx) : 0;
     const bool own = q < npx && paper_row_owned(y, rank, world);
     if (rgb8) { if (threadIdx.x == 0) s_any = 0; __syncthreads(); }
     if (own) {

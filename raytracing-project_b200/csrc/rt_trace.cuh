@@ -394,6 +394,9 @@ __device__ __forceinline__ void light_shade(int l, const float4 m0, float ks, fl
 //               bundle towards that light, one entry per lane, into its own mask words — no barrier, no shared atomics, and
 //               the warps of a CTA need not walk in step.
 enum { kListsNone = 0, kListsCta = 1, kListsWarp = 2 };
+#ifndef RT_SHADOW_RENORM
+#define RT_SHADOW_RENORM 0
+#endif
 template <bool C, bool K, bool M, bool G = false>
 __device__ __forceinline__ RGBf shade(bool lit, const int LISTS, const Hit& h, V3 p, V3 wo, Counters& cnt) {
     const float eps = fmaxf(1e-3f, 1e-4f * h.t);                             // shading.cpp:43
@@ -459,7 +462,9 @@ __device__ __forceinline__ RGBf shade(bool lit, const int LISTS, const Hit& h, V
             }
             if (need) {
                 ++cnt.shadow;
-                if (!occluded<C, K, M, G>(so, normalized(wi), eps, tmaxS, cb, cnt)) vis |= 1u << (l & 31);   // Ray ctor re-normalises (core.h:278)
+                // (the Ray ctor re-normalises its direction, core.h:278: in double that is the identity up to 1e-16; wi = L * rsqrt(|L|^2)
+                // is unit to 2 ulp already, and a second FP32 normalisation brings it no closer to the exact direction)
+                if (!occluded<C, K, M, G>(so, RT_SHADOW_RENORM ? normalized(wi) : wi, eps, tmaxS, cb, cnt)) vis |= 1u << (l & 31);
             }
             if (lists == kListsWarp) __syncwarp();                          // the words are rewritten for the next light
         }
