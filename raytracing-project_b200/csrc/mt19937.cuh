@@ -45,6 +45,18 @@ MT_HD uint32_t next_word(const uint32_t* old, int k) {
     uint32_t new396 = new169 ^ g(old[396], old[397]);
     return new396 ^ g(old[623], new0);
 }
+// One twist by the first 227 threads of a CTA, one barrier: thread t produces new[t], new[t + 227] and new[t + 454] — each
+// from the one before it, which it still holds in a register — so every word costs ONE g() instead of the 1 / 2 / 3 of
+// next_word (the render kernels' tile prologue: 1.9 -> 1 g per word).  Thread 169 also owns word 623.  `emit(k, w)` stores.
+template <class Emit>
+MT_HD void twist_by_thread(const uint32_t* old, int t, Emit emit) {
+    if (t >= 227) return;
+    const uint32_t n0 = old[t + 397] ^ g(old[t], old[t + 1]);
+    const uint32_t n1 = n0 ^ g(old[t + 227], old[t + 228]);
+    emit(t, n0); emit(t + 227, n1);
+    if (t < 169) emit(t + 454, n1 ^ g(old[t + 454], old[t + 455]));
+    if (t == 169) emit(623, n1 ^ g(old[623], old[397] ^ g(old[0], old[1])));      // s[623] = new[396] ^ g(old[623], new[0])
+}
 MT_HD uint32_t temper(uint32_t y) {
     y ^= y >> 11; y ^= (y << 7) & 0x9d2c5680u; y ^= (y << 15) & 0xefc60000u; y ^= y >> 18;
     return y;

@@ -67,8 +67,11 @@ int rt_debug_mt_block_host(uint32_t seed, uint64_t block, uint32_t* out624) {
     uint32_t a[mt::kN], b[mt::kN];
     mt::seed_state(seed, a);
     uint32_t *cur = a, *nxt = b;
+    // even blocks by the word-parallel form (next_word: the checkpoint / jump kernels), odd ones by the thread form of the
+    // render kernels' tile prologue (twist_by_thread): both must reproduce std::mt19937
     for (uint64_t i = 0; i <= block; ++i) {
-        for (int k = 0; k < mt::kN; ++k) nxt[k] = mt::next_word(cur, k);
+        if (i & 1) for (int t = 0; t < 227; ++t) mt::twist_by_thread(cur, t, [nxt](int k, uint32_t w) { nxt[k] = w; });
+        else for (int k = 0; k < mt::kN; ++k) nxt[k] = mt::next_word(cur, k);
         uint32_t* t = cur; cur = nxt; nxt = t;
     }
     for (int k = 0; k < mt::kN; ++k) out624[k] = mt::temper(cur[k]);

@@ -249,7 +249,8 @@ __global__ void __launch_bounds__(kRenderThreads, (!F && !K) ? RT_NONFLAT_BLOCKS
         __syncthreads();
 #pragma unroll 1
         for (int b = 0; b < mt::kTwistsPerTile; ++b) {
-            for (int k = tid; k < mt::kN; k += kRenderThreads) raw[(b + 1) * mt::kN + k] = mt::next_word(raw + b * mt::kN, k);
+            uint32_t* nw = raw + (b + 1) * mt::kN;
+            mt::twist_by_thread(raw + b * mt::kN, tid, [nw](int k, uint32_t w) { nw[k] = w; });
             __syncthreads();
         }
         if (M && RT_TILE_CAMERA_MASK) cnt.tests += cand_build(0, 1);         // the tile's camera mask (barrier inside)
@@ -385,9 +386,9 @@ __global__ void __launch_bounds__(kRenderThreads, RT_WAVE_BLOCKS) render_wavefro
             int cur = 0;
 #pragma unroll 1
             for (int b = 0; b < mt::kTwistsPerTile; ++b) {
-                for (int k = tid; k < mt::kN; k += kRenderThreads) {
-                    uint32_t w = mt::next_word(st[cur], k);
-                    st[cur ^ 1][k] = w; outw[b * mt::kN + k] = mt::temper(w);
+                {
+                    uint32_t* nw = st[cur ^ 1]; uint32_t* ow = outw + b * mt::kN;
+                    mt::twist_by_thread(st[cur], tid, [nw, ow](int k, uint32_t w) { nw[k] = w; ow[k] = mt::temper(w); });
                 }
                 __syncthreads();
                 cur ^= 1;
