@@ -467,6 +467,7 @@ int upload_scene(Context& cx, const rt_scene_desc* d, rt_scene** out) {
     rtd::SceneHeader& h = s->hdr;
     for (int k = 0; k < 3; ++k) { h.eye[k] = d->eye[k]; h.P[k] = d->screen_p[k]; h.bg[k] = d->background[k]; }
     h.lx = d->lx; h.ly = d->ly; h.nx = d->width; h.ny = d->height;
+    h.inv_nx = 1.0 / (double)d->width; h.inv_ny = 1.0 / (double)d->height;
     h.medium_index = d->medium_index; h.recursion = d->recursion;
     h.n_objects = d->n_objects; h.n_lights = d->n_dir_lights + d->n_lights; h.n_runs = (int)s->runs.size();
     h.obj_geom = (const float4*)(base + o_obj_geom); h.obj_meta = (const int4*)(base + o_obj_meta);

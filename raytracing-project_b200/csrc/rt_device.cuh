@@ -22,6 +22,7 @@ namespace rtd {
 
 struct SceneHeader {
     double eye[3], P[3], lx, ly;
+    double inv_nx, inv_ny;      // RN(1 / nx), RN(1 / ny): div_by() below
     int nx, ny;
     float bg[3]; float medium_index;
     int recursion, n_objects, n_lights, n_runs, n_leaves, n_ops, n_clusters;
@@ -267,7 +268,7 @@ __device__ __forceinline__ unsigned cand_build(int b0, int nb) {
         // A task = one bundle x `chunk` consecutive words: the bundle is set up once per task, and the tasks are sized so that
         // they spread evenly over the warps (snorlax: 5 lights x 2 words -> 5 tasks of 2 words instead of 10 tasks on 8 warps).
 #ifndef RT_CAND_CHUNK
-#define RT_CAND_CHUNK 0          // measured: snorlax 4K 10.50 (off) vs 10.72 ms (on)
+#define RT_CAND_CHUNK 0          // measured: snorlax 4K 10.50 (off) vs 10.72 ms (on); with the leaf-word skip: see DESIGN section 7
 #endif
         const int chunk = RT_CAND_CHUNK ? max(1, min(W, (nb * W + nwarps - 1) / nwarps)) : 1;
         const int per_bundle = (W + chunk - 1) / chunk;
@@ -282,7 +283,11 @@ __device__ __forceinline__ unsigned cand_build(int b0, int nb) {
                 bundle_from_box_light(B, lo, hi, eps_max, L, lp.w != 0.f);
             }
             const int w_end = min(W, (part + 1) * chunk);
+            // A task that covers the whole bundle culls the CSG leaves only if one of the bundle's generic objects (the
+            // programs that own them) stayed a candidate: nobody reads the leaf words otherwise.
+            bool leaves_needed = !(RT_CAND_CHUNK && chunk == W);
             for (int w = part * chunk; w < w_end; ++w) {
+                if (w >= c_hdr.cull_leaf_word && !leaves_needed) break;
                 const float4 g = __ldg(c_hdr.cull_geom + 32 * w + lane);
                 const bool plane = (__ldg(c_hdr.cull_plane_bits + w) >> lane) & 1u;
                 Sphere4 q; q.x = g.x; q.y = g.y; q.z = g.z; q.w = g.w;
@@ -293,6 +298,7 @@ __device__ __forceinline__ unsigned cand_build(int b0, int nb) {
                 ++tests;
                 const uint32_t bits = __ballot_sync(kFullWarp, cand);
                 if (lane == 0) cand_words(b)[w] = bits;
+                if (RT_CAND_CHUNK && w < c_hdr.cull_leaf_word && (bits & __ldg(c_hdr.cull_plane_bits + 2 * W + w))) leaves_needed = true;
             }
             part += nwarps;
             while (part >= per_bundle) { part -= per_bundle; ++bb; }

@@ -26,3 +26,4 @@ timeout -k 10 300 python scripts/profile_run.py scenes/penguin_4k.json paper 2 >
 timeout -k 10 600 ncu --set full --clock-control none --import-source on -k regex:paper_ -s 2 -c 2 -o $OUT/prof_penguin_4k_paper \
     python scripts/profile_run.py scenes/penguin_4k.json paper 2 > $OUT/ncu_prof_paper.log 2>&1
 ls $OUT | tr '\n' ' '
+timeout -k 10 600 python bench.py --steps 2 --warmup 3 --no-cpu --scene scenes/synthetic_b_16k.json > $OUT/bench_synthetic_b_16k.json 2> $OUT/bench_synthetic_b_16k.err; grep -o '"ms_per_step": [0-9.]*' $OUT/bench_synthetic_b_16k.json
