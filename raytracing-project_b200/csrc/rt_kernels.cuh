@@ -402,9 +402,17 @@ __global__ void __launch_bounds__(kRenderThreads, RT_WAVE_BLOCKS) render_wavefro
             int cur = 0;
 #pragma unroll 1
             for (int b = 0; b < mt::kTwistsPerTile; ++b) {
-                {
+#ifndef RT_WAVE_TWIST_THREADS
+#define RT_WAVE_TWIST_THREADS 1
+#endif
+                if (RT_WAVE_TWIST_THREADS) {
                     uint32_t* nw = st[cur ^ 1]; uint32_t* ow = outw + b * mt::kN;
                     mt::twist_by_thread(st[cur], tid, [nw, ow](int k, uint32_t w) { nw[k] = w; ow[k] = mt::temper(w); });
+                } else {
+                    for (int k = tid; k < mt::kN; k += kRenderThreads) {
+                        uint32_t w = mt::next_word(st[cur], k);
+                        st[cur ^ 1][k] = w; outw[b * mt::kN + k] = mt::temper(w);
+                    }
                 }
                 __syncthreads();
                 cur ^= 1;
