@@ -36,19 +36,19 @@ struct GridHeader {
 };
 struct GridWords { uint32_t x, y, z, w; };                                 // uint4 on the device
 
-// ORs into `out` the masks of the cells the segment o + t d, t in [tmin, tmax], crosses.  Returns the number of cells
-// visited (0: the segment misses the grid box; -1: NaN in the ray, the caller must take every sphere).  Everything lives in
-// scalars (no array is indexed by the stepping axis: that would put the walk's state into local memory).
-// `cell(i)` returns the four words of cell i (a shared-memory or read-only global load on the device, an array on the host).
-template <class CellLoad>
-RT_GRID_FN int grid_walk(const GridHeader& g, CellLoad cell, const float o[3], const float d[3], float tmin, float tmax, GridWords& out) {
+// Walks the cells the segment o + t d, t in [tmin, tmax], crosses, FRONT TO BACK, and calls visit(words, t1) for the ALWAYS
+// cell and then for every cell; `t1` is the far end of the segment and the visitor may lower it — to its closest hit so far
+// (no sphere can be hit before the next cell's entry that was not a candidate of a visited cell: a hit point lies in a visited
+// cell), or to -inf to stop.  Returns the number of cells visited (0: the segment misses the grid box; -1: NaN in the ray, no
+// statement, no visit).  Everything lives in scalars (no array is indexed by the stepping axis: that would put the walk's
+// state into local memory).  `cell(i)` returns the four words of cell i (shared-memory or read-only global load on the
+// device, an array on the host).
+template <class CellLoad, class Visit>
+RT_GRID_FN int grid_visit(const GridHeader& g, CellLoad cell, const float o[3], const float d[3], float tmin, float tmax, Visit visit) {
     const float s = o[0] + o[1] + o[2] + d[0] + d[1] + d[2] + tmin;
     if (!(s == s) || !(tmax == tmax)) return -1;                       // NaN (or inf - inf): no statement about the ray
-    {   // the spheres that are not binned
-        const GridWords m = cell(g.n[0] * g.n[1] * g.n[2]);
-        out.x |= m.x; out.y |= m.y; out.z |= m.z; out.w |= m.w;
-    }
     float t0 = tmin, t1 = tmax;
+    visit(cell(g.n[0] * g.n[1] * g.n[2]), t1);                          // the spheres that are not binned
     float inv[3];
 #pragma unroll
     for (int a = 0; a < 3; ++a) {
@@ -63,6 +63,7 @@ RT_GRID_FN int grid_walk(const GridHeader& g, CellLoad cell, const float o[3], c
     }
     // (the binned boxes lie at least a cell's pad inside the grid box: the rounding of this interval cannot lose a hit)
     if (!(t0 <= t1)) return 0;
+    const float t_slab = t1;                                              // the visitor lowers t1 below the box's far side only
     int ix[3], step[3]; float tnext[3], tdelta[3];
 #pragma unroll
     for (int a = 0; a < 3; ++a) {
@@ -84,8 +85,8 @@ RT_GRID_FN int grid_walk(const GridHeader& g, CellLoad cell, const float o[3], c
     const int limit = nx + ny + nz + 3;                                   // (a walk crosses at most nx + ny + nz cells)
     int visited = 0;
     for (;;) {
-        const GridWords m = cell((z * ny + y) * nx + x);
-        out.x |= m.x; out.y |= m.y; out.z |= m.z; out.w |= m.w;
+        visit(cell((z * ny + y) * nx + x), t1);
+        t1 = fminf(t1, t_slab);
         ++visited;
         // next cell along the axis whose boundary comes first
         const bool sx = tx <= ty && tx <= tz, sy = !sx && ty <= tz, sz = !sx && !sy;
@@ -96,6 +97,12 @@ RT_GRID_FN int grid_walk(const GridHeader& g, CellLoad cell, const float o[3], c
         tx += sx ? tdelta[0] : 0.f; ty += sy ? tdelta[1] : 0.f; tz += sz ? tdelta[2] : 0.f;
     }
     return visited;
+}
+
+// The plain form: ORs the masks of every cell the segment crosses into `out`.
+template <class CellLoad>
+RT_GRID_FN int grid_walk(const GridHeader& g, CellLoad cell, const float o[3], const float d[3], float tmin, float tmax, GridWords& out) {
+    return grid_visit(g, cell, o, d, tmin, tmax, [&out](const GridWords& m, float&) { out.x |= m.x; out.y |= m.y; out.z |= m.z; out.w |= m.w; });
 }
 
 }  // namespace rtd

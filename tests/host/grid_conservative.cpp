@@ -2,7 +2,8 @@
 // glass scene, random clouds, mixed radii, several scales) and random segments — origins inside and outside the grid,
 // random / axis-parallel / near-tangent directions, finite and infinite windows — every sphere that the device's exact FP32
 // test (sphere_disc / sphere_t of csrc/rt_device.cuh, restated below with the same fmaf sequence) accepts inside the window
-// has its bit set in the words grid_walk returns.  Prints "<rays> <accepted sphere hits> <mean cells per ray x 100>
+// has its bit set in the words grid_walk returns, and the front-to-back walk with early exit finds the same closest hit (and
+// the same any-hit answer) as the sequential scan.  Prints "<rays> <accepted sphere hits> <mean cells per ray x 100>
 // <mean candidate bits per ray x 100> <violations>"; test infrastructure only (tests/test_grid.py builds and runs it).
 #include <cmath>
 #include <cstdio>
@@ -88,6 +89,34 @@ int main(int argc, char** argv) {
             const int visited = rtd::grid_walk(g, [mp](int c) { return rtd::GridWords{mp[4 * c], mp[4 * c + 1], mp[4 * c + 2], mp[4 * c + 3]}; }, oo, dd, tmin, tmax, gwd);
             const uint32_t w[rtd::kGridMaxWords] = {gwd.x, gwd.y, gwd.z, gwd.w};
             ++rays; cells += visited > 0 ? visited : 0;
+            // closest hit: the sequential scan of scene.cpp:10-24 (index order, inclusive shrinking window: the later index
+            // wins an exact tie) against the front-to-back walk with early exit (rt_trace.cuh scan_body), and any hit
+            if (visited >= 0) {
+                int sb = -1; float st = tmax;
+                for (int i = 0; i < n; ++i) { float t; if (sphere_t(sph.data() + 4 * i, o, d, tmin, st, t)) { sb = i; st = t; } }
+                for (int any = 0; any < 2; ++any) {
+                    int wb = -1; float wt = tmax; uint32_t tested[4] = {0, 0, 0, 0};
+                    rtd::grid_visit(g, [mp](int c) { return rtd::GridWords{mp[4 * c], mp[4 * c + 1], mp[4 * c + 2], mp[4 * c + 3]}; }, oo, dd, tmin, tmax,
+                        [&](const rtd::GridWords& m, float& t1) {
+                            const uint32_t mw[4] = {m.x, m.y, m.z, m.w};
+                            for (int w2 = 0; w2 < g.words; ++w2) {
+                                uint32_t b2 = mw[w2] & ~tested[w2];
+                                while (b2) {
+                                    const int dev = 32 * w2 + __builtin_ctz(b2); b2 &= b2 - 1;
+                                    const int i = dev - shift;
+                                    float t;
+                                    if (i < 0 || i >= n || !sphere_t(sph.data() + 4 * i, o, d, tmin, wt, t)) continue;
+                                    if (t == wt && i < wb) continue;
+                                    wb = i; wt = t;
+                                }
+                                tested[w2] |= mw[w2];
+                            }
+                            t1 = (any && wb >= 0) ? -INFINITY : fminf(t1, wt);
+                        });
+                    const bool ok = any ? ((wb >= 0) == (sb >= 0)) : (wb == sb && (sb < 0 || wt == st));
+                    if (!ok && ++bad <= 5) fprintf(stderr, "CLOSEST scene %d ray %d any %d: scan %d %g walk %d %g\n", sc, r, any, sb, st, wb, wt);
+                }
+            }
             for (int ww = 0; ww < g.words; ++ww) bits += __builtin_popcount(w[ww]);
             for (int i = 0; i < n; ++i) {
                 float t;
